@@ -1,0 +1,184 @@
+// bqa_evolver.cuh - whole-task adaptive evolution on ONE execution context.
+//
+// This is north_star kernel (5) ("batched small-state kernels that evolve many parameter-sweep tasks
+// per launch") together with kernel (2) (DOPRI5/DOP853 stage combine + error norm, step resident on
+// the GPU): one CTA owns one task and runs the whole AnalogGate._apply /
+// _apply_interaction_picture flow (emulate/ir/state_vector.py:574-641) - including SciPy's restart
+// at every requested output time - without returning to the host.
+//
+// Ctx contract (device: one CTA, bqa_small.cuh; host: serial loop, tests/hostsim):
+//   for_each(n, f)   run f(i) for all 0 <= i < n, partitioned over the context's threads
+//   sync()           barrier + memory visibility inside the context
+//   sum1/2/3(...)    replace each thread's partial by the total over the context (same value and
+//                    same summation order in every thread, so control flow stays uniform)
+//   single(f)        f() executed by exactly one thread, followed by a barrier
+#pragma once
+#include "bqa_core.cuh"
+
+namespace bqa {
+
+// vec[0] = y (current solution), vec[1] = ys (stage input / gather source), vec[2+s] = K slot s.
+// The table itself lives in shared memory on the GPU so that slot indices read from the Butcher
+// tables can index it dynamically without spilling pointers to local memory.
+constexpr int kVecY = 0;
+constexpr int kVecYs = 1;
+constexpr int kVecK = 2;
+constexpr int kNumVec = 12;
+
+struct Workspace {
+  cplx** vec;     // [kNumVec] pointer table (shared)
+  Coefs* coefs;   // shared scratch for the per-call coefficients
+};
+
+template <class Ctx>
+struct TaskEvolver {
+  Ctx& ctx;
+  const PlanView& P;
+  TaskView tv;
+  const double* V;   // static (Rydberg) diagonal or nullptr
+  Workspace w;
+  SolverOpts o;
+  Controller c;
+
+  BQA_HD TaskEvolver(Ctx& ctx_, const PlanView& P_, const double* rec, const double* V_, Workspace w_,
+                     SolverOpts o_)
+      : ctx(ctx_), P(P_), tv(task_view(rec)), V(V_), w(w_), o(o_) {}
+
+  BQA_HD cplx* y() const { return w.vec[kVecY]; }
+  BQA_HD cplx* ys() const { return w.vec[kVecYs]; }
+  BQA_HD cplx* k(int s) const { return w.vec[kVecK + s]; }
+  BQA_HD bool rotating() const { return o.interaction != 0 && V != nullptr; }
+
+  BQA_HD void swap_vec(int a, int b) {
+    cplx** vec = w.vec;
+    ctx.single([&]() {
+      cplx* t = vec[a];
+      vec[a] = vec[b];
+      vec[b] = t;
+    });
+  }
+
+  BQA_HD void eval_coefs(double t) {
+    int ne = tv.n_atoms * (P.n_level - 1);
+    Coefs* cf = w.coefs;
+    const TaskView& tvr = tv;
+    const PlanView& Pr = P;
+    ctx.for_each(ne + P.n_csr, [&](int64_t e) {
+      if (e < ne)
+        coef_entry(tvr, t, (int)e, *cf);
+      else
+        coef_csr_entry(Pr, tvr, t, (int)(e - ne), *cf);
+    });
+    ctx.sync();
+  }
+
+  // kout = f(t, .) evaluated on the stage input held in ys (already multiplied by u(t) in the
+  // interaction picture)
+  BQA_HD void rhs_from_ys(double t, cplx* kout) {
+    eval_coefs(t);
+    const PlanView& Pr = P;
+    const Coefs& cf = *w.coefs;
+    const cplx* in = ys();
+    const double* Vd = V;
+    const bool inter = o.interaction != 0;
+    ctx.for_each(P.dim, [&](int64_t i) {
+      cplx hz = h_apply_dispatch(Pr, cf, inter ? nullptr : Vd, in, i);
+      if (inter && Vd) hz = cmul_conj_a(phase_u(Vd[i], t), hz);
+      kout[i] = times_minus_i(hz);
+    });
+    ctx.sync();
+  }
+
+  // ys = (u(t) *) [ y + h * sum_j val[j] * K[slot[j]] ]     (nnz = 0: ys = (u(t)*) y)
+  BQA_HD void stage_input(double t, double h, int nnz, const int* slot, const double* val) {
+    cplx* out = ys();
+    const cplx* yy = y();
+    cplx* const* kk = w.vec + kVecK;
+    const double* Vd = V;
+    const bool rot = rotating();
+    ctx.for_each(P.dim, [&](int64_t i) {
+      double sr = 0.0, si = 0.0;
+      for (int j = 0; j < nnz; ++j) {
+        cplx kz = kk[slot[j]][i];
+        sr += val[j] * kz.re;
+        si += val[j] * kz.im;
+      }
+      cplx z = cmake(yy[i].re + h * sr, yy[i].im + h * si);
+      out[i] = rot ? cmul(phase_u(Vd[i], t), z) : z;
+    });
+    ctx.sync();
+  }
+
+  // automatic initial step (Hairer HINIT); K[0] = f(x, y) must be valid.  Uses K[1] as f1.
+  BQA_HD void hinit() {
+    const cplx* yy = y();
+    const cplx* f0 = k(0);
+    double dnf = 0.0, dny = 0.0;
+    const double atol = o.atol, rtol = o.rtol;
+    ctx.for_each(P.dim, [&](int64_t i) {
+      double sk = atol + rtol * fabs(yy[i].re);
+      double a = f0[i].re / sk, b = yy[i].re / sk;
+      dnf += a * a;
+      dny += b * b;
+      sk = atol + rtol * fabs(yy[i].im);
+      a = f0[i].im / sk;
+      b = yy[i].im / sk;
+      dnf += a * a;
+      dny += b * b;
+    });
+    ctx.sum2(dnf, dny);
+    double h0 = c.hinit_first(dnf, dny);
+    const int one_slot[1] = {0};
+    const double one_val[1] = {1.0};
+    stage_input(c.x + h0, h0, 1, one_slot, one_val);  // y1 = y + h0 * f0
+    rhs_from_ys(c.x + h0, k(1));
+    const cplx* f1 = k(1);
+    double der2 = 0.0;
+    ctx.for_each(P.dim, [&](int64_t i) {
+      double sk = atol + rtol * fabs(yy[i].re);
+      double a = (f1[i].re - f0[i].re) / sk;
+      der2 += a * a;
+      sk = atol + rtol * fabs(yy[i].im);
+      a = (f1[i].im - f0[i].im) / sk;
+      der2 += a * a;
+    });
+    ctx.sum1(der2);
+    c.hinit_finish(o, h0, dnf, der2);
+  }
+
+  BQA_HD void step_dopri5(int& accepted);
+  BQA_HD void step_dop853(int& accepted);
+
+  // one integrate(x0 -> x1) call of scipy's ode (a fresh start: k1, hinit, counters)
+  BQA_HD void integrate(double x0, double x1) {
+    c.begin(o, x0, x1);
+    stage_input(x0, 0.0, 0, nullptr, nullptr);
+    rhs_from_ys(x0, k(0));
+    hinit();
+    while (!c.done) {
+      if (!c.step_begin(o)) break;
+      int accepted = 0;
+      if (o.solver == kSolverDopri5)
+        step_dopri5(accepted);
+      else
+        step_dop853(accepted);
+      c.step_end(o, accepted);
+    }
+  }
+
+  // Schroedinger-picture state at the current time into `out` (SV:636-638 for the rotation)
+  BQA_HD void emit_state(double t, cplx* out) {
+    const cplx* yy = y();
+    const double* Vd = V;
+    const bool rot = rotating();
+    ctx.for_each(P.dim, [&](int64_t i) {
+      cplx z = yy[i];
+      out[i] = rot ? cmul(phase_u(Vd[i], t), z) : z;
+    });
+    ctx.sync();
+  }
+};
+
+}  // namespace bqa
+
+#include "bqa_evolver_steps.cuh"
