@@ -1,0 +1,233 @@
+// bqa_api_evolve.cuh - batched evolution entry points (included from bqa_api_ops.cuh)
+#pragma once
+
+#include "bqa_large.cuh"
+#include "bqa_large_host.cuh"
+
+// smem priority of the 12 vectors: ys first (every gather reads it), then k1, then the K slots that
+// are re-read by the most stage combines, then y.
+static const int kOrder853[kNumVec] = {kVecYs, kVecK + 0, kVecK + 3, kVecK + 4, kVecY, kVecK + 5,
+                                       kVecK + 6, kVecK + 7, kVecK + 8, kVecK + 9, kVecK + 1, kVecK + 2};
+static const int kOrder5[kNumVec] = {kVecYs, kVecK + 0, kVecK + 1, kVecY, kVecK + 6, kVecK + 2,
+                                     kVecK + 3, kVecK + 4, kVecK + 5, kVecK + 7, kVecK + 8, kVecK + 9};
+
+template <int kThreads>
+static int launch_small(bqa_plan* p, SmallArgs& A, int n_tasks) {
+  auto kern = evolve_small_kernel<kThreads>;
+  cudaFuncAttributes fa;
+  CK(cudaFuncGetAttributes(&fa, kern));
+  const int64_t vec_bytes = (int64_t)sizeof(cplx) * A.P.dim;
+  const int64_t dyn_max = p->smem_optin - (int64_t)fa.sharedSizeBytes - 1024;
+  int n_smem = (int)std::min<int64_t>(A.n_vec, dyn_max / vec_bytes);
+  if (n_smem < 0) n_smem = 0;
+  // tiny states: leave room for several CTAs per SM instead of hoarding shared memory
+  size_t dyn = (size_t)n_smem * vec_bytes;
+  CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(dyn, 1024)));
+  int occ = 1;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, dyn));
+  if (occ < 1) return fail("evolve kernel does not fit on an SM (threads=%d, smem=%zu)", kThreads, dyn);
+  const int grid = (int)std::min<int64_t>(n_tasks, (int64_t)occ * p->sm_count);
+  A.n_smem_vecs = n_smem;
+  A.gws_stride = (int64_t)(A.n_vec - n_smem) * A.P.dim;
+  cplx* gws = nullptr;
+  if (A.gws_stride > 0) {
+    CK(cudaMalloc(&gws, sizeof(cplx) * A.gws_stride * grid));
+  }
+  A.gws = gws;
+  kern<<<grid, kThreads, dyn, p->stream>>>(A);
+  LAUNCHED();
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+  if (gws) cudaFree(gws);
+  if (e != cudaSuccess) return fail("evolve_small_kernel: %s", cudaGetErrorString(e));
+  return 0;
+}
+
+// all pointers are device pointers; h_times (host copy) is used for the longest-first ordering
+static int evolve_small_device(bqa_plan* p, const double* d_records, const int64_t* d_offsets, int n_tasks,
+                               const bqa_solver_opts* o, const cplx* d_psi0, int psi0_mode, const double* d_times,
+                               const double* h_times, int n_times, cplx* d_out, TaskStats* d_stats) {
+  SmallArgs A;
+  memset(&A, 0, sizeof(A));
+  A.P = p->P;
+  A.diags = p->d_diag_table;
+  A.n_diags = (int)p->diags.size();
+  A.records = d_records;
+  A.offsets = d_offsets;
+  A.n_tasks = n_tasks;
+  A.psi0 = d_psi0;
+  A.psi0_mode = psi0_mode;
+  A.times = d_times;
+  A.n_times = n_times;
+  A.out = d_out;
+  A.stats = d_stats;
+  A.o = default_opts(o->solver, o->atol, o->rtol, o->nsteps, o->interaction_picture);
+  A.o.reject_mode = o->reject_mode;
+  const bool d5 = o->solver == BQA_SOLVER_DOPRI5;
+  A.n_vec = d5 ? 9 : 12;
+  memcpy(A.vec_order, d5 ? kOrder5 : kOrder853, sizeof(A.vec_order));
+  // work queue: longest final time first
+  std::vector<int32_t> order(n_tasks);
+  std::iota(order.begin(), order.end(), 0);
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
+    return h_times[(size_t)a * n_times + n_times - 1] > h_times[(size_t)b * n_times + n_times - 1];
+  });
+  int32_t* d_order = nullptr;
+  int* d_counter = nullptr;
+  CK(cudaMalloc(&d_order, sizeof(int32_t) * n_tasks + sizeof(int)));
+  d_counter = (int*)(d_order + n_tasks);
+  CK(cudaMemcpyAsync(d_order, order.data(), sizeof(int32_t) * n_tasks, cudaMemcpyHostToDevice, p->stream));
+  CK(cudaMemsetAsync(d_counter, 0, sizeof(int), p->stream));
+  A.order = d_order;
+  A.counter = d_counter;
+  const int64_t dim = p->P.dim;
+  int rc;
+  if (dim <= 256)
+    rc = launch_small<128>(p, A, n_tasks);
+  else if (dim <= 1024)
+    rc = launch_small<256>(p, A, n_tasks);
+  else if (dim <= 2048)
+    rc = launch_small<512>(p, A, n_tasks);
+  else
+    rc = launch_small<1024>(p, A, n_tasks);
+  cudaFree(d_order);
+  return rc;
+}
+
+static int check_opts(const bqa_solver_opts* o) {
+  if (!o) return fail("null solver options");
+  if (o->solver != BQA_SOLVER_DOPRI5 && o->solver != BQA_SOLVER_DOP853)
+    return fail("solver %d not supported (dop853 = 8, dopri5 = 5; lsoda has no GPU implementation)", o->solver);
+  if (!(o->atol >= 0.0) || !(o->rtol >= 0.0) || (o->atol == 0.0 && o->rtol == 0.0)) return fail("bad tolerances");
+  return 0;
+}
+
+// pick the engine: the CTA-per-task kernel for batches / small states, the streamed kernels for one
+// large state
+static int pick_engine(const bqa_plan* p, const bqa_solver_opts* o, int n_tasks) {
+  if (o->engine == BQA_ENGINE_CTA_PER_TASK || o->engine == BQA_ENGINE_STREAMED) return o->engine;
+  if (p->P.dim <= 8192) return BQA_ENGINE_CTA_PER_TASK;
+  if ((int64_t)n_tasks >= p->sm_count && p->P.dim <= 65536) return BQA_ENGINE_CTA_PER_TASK;
+  return BQA_ENGINE_STREAMED;
+}
+
+static int evolve_any_device(bqa_plan* p, const double* d_records, const int64_t* d_offsets,
+                             const std::vector<int64_t>& h_offsets, const double* h_records, int n_tasks,
+                             const bqa_solver_opts* o, const cplx* d_psi0, int psi0_mode, const double* d_times,
+                             const double* h_times, int n_times, cplx* d_out, TaskStats* d_stats) {
+  const int engine = pick_engine(p, o, n_tasks);
+  if (engine == BQA_ENGINE_CTA_PER_TASK)
+    return evolve_small_device(p, d_records, d_offsets, n_tasks, o, d_psi0, psi0_mode, d_times, h_times, n_times,
+                               d_out, d_stats);
+  return evolve_large_device(p, d_records, h_offsets, h_records, n_tasks, o, d_psi0, psi0_mode, h_times, n_times,
+                             d_out, d_stats);
+}
+
+extern "C" {
+
+int bqa_evolve_batch(bqa_plan* p, const double* records, const int64_t* offsets, int32_t n_tasks,
+                     const bqa_solver_opts* o, const void* psi0, int32_t psi0_shared, const double* times,
+                     int32_t n_times, void* psi_out, bqa_task_stats* stats, int32_t mem) {
+  if (!p || !records || !offsets || !times || n_tasks < 1 || n_times < 1) return fail("bqa_evolve_batch: bad argument");
+  if (check_opts(o)) return 1;
+  const int64_t dim = p->P.dim;
+  // host copies of the small control arrays (needed for scheduling whatever `mem` is)
+  std::vector<int64_t> h_off(n_tasks + 1);
+  std::vector<double> h_times((size_t)n_tasks * n_times);
+  if (mem == BQA_MEM_DEVICE) {
+    CK(cudaMemcpy(h_off.data(), offsets, sizeof(int64_t) * (n_tasks + 1), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(h_times.data(), times, sizeof(double) * h_times.size(), cudaMemcpyDeviceToHost));
+  } else {
+    memcpy(h_off.data(), offsets, sizeof(int64_t) * (n_tasks + 1));
+    memcpy(h_times.data(), times, sizeof(double) * h_times.size());
+  }
+  std::vector<double> h_rec_copy;
+  const double* h_records = records;
+  if (mem == BQA_MEM_DEVICE && pick_engine(p, o, n_tasks) == BQA_ENGINE_STREAMED) {
+    h_rec_copy.resize(h_off[n_tasks]);
+    CK(cudaMemcpy(h_rec_copy.data(), records, sizeof(double) * h_rec_copy.size(), cudaMemcpyDeviceToHost));
+    h_records = h_rec_copy.data();
+  }
+  Staged rec, off, tm, p0, out, st;
+  if (rec.in(records, sizeof(double) * h_off[n_tasks], mem, p->stream)) return 1;
+  if (off.in(offsets, sizeof(int64_t) * (n_tasks + 1), mem, p->stream)) return 1;
+  if (tm.in(times, sizeof(double) * h_times.size(), mem, p->stream)) return 1;
+  const int psi0_mode = psi0 ? (psi0_shared ? 1 : 2) : 0;
+  if (p0.in(psi0, sizeof(cplx) * dim * (psi0_mode == 2 ? n_tasks : 1), mem, p->stream)) return 1;
+  if (out.out(psi_out, sizeof(cplx) * dim * (size_t)n_tasks * n_times, mem)) return 1;
+  if (st.out(stats, sizeof(TaskStats) * (size_t)n_tasks * n_times, BQA_MEM_HOST)) return 1;
+  if (evolve_any_device(p, (const double*)rec.dev, (const int64_t*)off.dev, h_off, h_records, n_tasks, o,
+                        (const cplx*)p0.dev, psi0_mode, (const double*)tm.dev, h_times.data(), n_times,
+                        (cplx*)out.dev, (TaskStats*)st.dev))
+    return 1;
+  if (out.flush(p->stream)) return 1;
+  if (st.flush(p->stream)) return 1;
+  CK(cudaStreamSynchronize(p->stream));
+  return 0;
+}
+
+int bqa_run_batch(bqa_plan* p, const double* records, const int64_t* offsets, int32_t n_tasks,
+                  const bqa_solver_opts* o, const double* times, const double* uniforms, int32_t n_shots,
+                  int32_t project, uint8_t* shots, void* psi_out, bqa_task_stats* stats, int32_t mem) {
+  if (!p || !records || !offsets || !times || !uniforms || !shots || n_tasks < 1 || n_shots < 1)
+    return fail("bqa_run_batch: bad argument");
+  if (check_opts(o)) return 1;
+  const int64_t dim = p->P.dim;
+  std::vector<int64_t> h_off(n_tasks + 1);
+  std::vector<double> h_times((size_t)n_tasks);
+  if (mem == BQA_MEM_DEVICE) {
+    CK(cudaMemcpy(h_off.data(), offsets, sizeof(int64_t) * (n_tasks + 1), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(h_times.data(), times, sizeof(double) * n_tasks, cudaMemcpyDeviceToHost));
+  } else {
+    memcpy(h_off.data(), offsets, sizeof(int64_t) * (n_tasks + 1));
+    memcpy(h_times.data(), times, sizeof(double) * n_tasks);
+  }
+  std::vector<double> h_rec_copy;
+  const double* h_records = records;
+  if (mem == BQA_MEM_DEVICE && pick_engine(p, o, n_tasks) == BQA_ENGINE_STREAMED) {
+    h_rec_copy.resize(h_off[n_tasks]);
+    CK(cudaMemcpy(h_rec_copy.data(), records, sizeof(double) * h_rec_copy.size(), cudaMemcpyDeviceToHost));
+    h_records = h_rec_copy.data();
+  }
+  Staged rec, off, tm, un, sh, st, psi;
+  if (rec.in(records, sizeof(double) * h_off[n_tasks], mem, p->stream)) return 1;
+  if (off.in(offsets, sizeof(int64_t) * (n_tasks + 1), mem, p->stream)) return 1;
+  if (tm.in(times, sizeof(double) * n_tasks, mem, p->stream)) return 1;
+  if (un.in(uniforms, sizeof(double) * (size_t)n_tasks * n_shots, mem, p->stream)) return 1;
+  if (sh.out(shots, (size_t)n_tasks * n_shots * p->P.n_atoms, mem)) return 1;
+  if (st.out(stats, sizeof(TaskStats) * (size_t)n_tasks, BQA_MEM_HOST)) return 1;
+  // final states: the caller's buffer, or an internal one
+  if (psi_out) {
+    if (psi.out(psi_out, sizeof(cplx) * dim * (size_t)n_tasks, mem)) return 1;
+  } else {
+    if (psi.out((void*)1, sizeof(cplx) * dim * (size_t)n_tasks, BQA_MEM_HOST)) return 1;
+    psi.host = nullptr;
+  }
+  if (evolve_any_device(p, (const double*)rec.dev, (const int64_t*)off.dev, h_off, h_records, n_tasks, o, nullptr, 0,
+                        (const double*)tm.dev, h_times.data(), 1, (cplx*)psi.dev, (TaskStats*)st.dev))
+    return 1;
+  // result.normalize() (SV:697) then result.sample(shots) (SV:699)
+  {
+    const int blocks = grid_for(p, dim, 256, 1);
+    double* partial = nullptr;
+    CK(cudaMalloc(&partial, sizeof(double) * ((size_t)blocks * n_tasks + n_tasks)));
+    double* n2 = partial + (size_t)blocks * n_tasks;
+    int rc = norm2_segments(p, (const cplx*)psi.dev, n_tasks, partial, blocks, n2);
+    if (!rc) {
+      scale_by_norm_kernel<<<dim3(blocks, n_tasks), 256, 0, p->stream>>>((cplx*)psi.dev, dim, dim, n2);
+      LAUNCHED();
+      rc = sample_device(p, (const cplx*)psi.dev, n_tasks, (const double*)un.dev, n_shots, project, (uint8_t*)sh.dev);
+    }
+    cudaError_t e = cudaStreamSynchronize(p->stream);
+    cudaFree(partial);
+    if (rc) return 1;
+    if (e != cudaSuccess) return fail("bqa_run_batch: %s", cudaGetErrorString(e));
+  }
+  if (sh.flush(p->stream)) return 1;
+  if (psi.flush(p->stream)) return 1;
+  if (st.flush(p->stream)) return 1;
+  CK(cudaStreamSynchronize(p->stream));
+  return 0;
+}
+
+}  // extern "C"

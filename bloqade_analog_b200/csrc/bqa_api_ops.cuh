@@ -1,0 +1,231 @@
+// bqa_api_ops.cuh - C ABI entry points that launch kernels (included at the end of bqa_api.cu)
+#pragma once
+
+static int grid_for(const bqa_plan* p, int64_t n, int threads, int per_sm = 8) {
+  int64_t want = (n + threads - 1) / threads;
+  int64_t cap = (int64_t)p->sm_count * per_sm;  // a multiple of the SM count
+  return (int)std::max<int64_t>(1, std::min(want, cap));
+}
+
+// segment-wise |psi|^2 sums -> d_out[n_seg] (two deterministic passes)
+static int norm2_segments(bqa_plan* p, const cplx* d_psi, int n_seg, double* d_partial, int blocks, double* d_out) {
+  dim3 g(blocks, n_seg);
+  norm2_partial_kernel<<<g, 256, 0, p->stream>>>(d_psi, p->P.dim, p->P.dim, d_partial);
+  LAUNCHED();
+  finish_sum_kernel<<<n_seg, 256, 0, p->stream>>>(d_partial, blocks, 1, d_out);
+  LAUNCHED();
+  CK(cudaGetLastError());
+  return 0;
+}
+
+// Born sampling of n_seg device states; all pointers device
+static int sample_device(bqa_plan* p, const cplx* d_psi, int n_seg, const double* d_uniforms, int n_shots,
+                         int project, uint8_t* d_shots) {
+  const int64_t dim = p->P.dim;
+  const int n_tiles = (int)((dim + kScanTile - 1) / kScanTile);
+  void* sc = nullptr;
+  size_t need = sizeof(double) * ((size_t)n_seg * n_tiles + n_seg + (size_t)n_seg * dim);
+  if (plan_scratch(p, need, &sc)) return 1;
+  double* tile_sums = (double*)sc;
+  double* totals = tile_sums + (size_t)n_seg * n_tiles;
+  double* cdf = totals + n_seg;
+  dim3 g(n_tiles, n_seg);
+  scan_tile_sums_kernel<<<g, kScanThreads, 0, p->stream>>>(d_psi, dim, dim, n_tiles, tile_sums);
+  LAUNCHED();
+  scan_tile_offsets_kernel<<<n_seg, 1024, 0, p->stream>>>(tile_sums, n_tiles, totals);
+  LAUNCHED();
+  scan_write_cdf_kernel<<<g, kScanThreads, 0, p->stream>>>(d_psi, dim, dim, n_tiles, tile_sums, totals, cdf);
+  LAUNCHED();
+  dim3 gs((n_shots + 127) / 128, n_seg);
+  const int project_flag = (project && p->P.n_level == 3) ? 1 : 0;
+  sample_search_kernel<<<gs, 128, 0, p->stream>>>(cdf, dim, p->P.configs, p->P.n_atoms, p->P.n_level, project_flag,
+                                                  d_uniforms, n_shots, d_shots);
+  LAUNCHED();
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" {
+
+int bqa_plan_add_csr(bqa_plan* p, int32_t amp_wf, int32_t phase_wf, int64_t nnz, const double* data,
+                     const int32_t* indices, const int64_t* indptr) {
+  if (!p || !data || !indices || !indptr) return fail("bqa_plan_add_csr: null argument");
+  if (p->csr.size() >= 8) return fail("bqa_plan_add_csr: at most 8 generic terms");
+  const int64_t dim = p->P.dim;
+  // transpose on the host (CSC of M read as CSR of M^T) so the device only ever gathers
+  std::vector<int64_t> t_indptr(dim + 1, 0);
+  for (int64_t j = 0; j < nnz; ++j) t_indptr[indices[j] + 1]++;
+  for (int64_t i = 0; i < dim; ++i) t_indptr[i + 1] += t_indptr[i];
+  std::vector<int32_t> t_indices(nnz);
+  std::vector<double> t_data(nnz);
+  std::vector<int64_t> fill(t_indptr.begin(), t_indptr.end() - 1);
+  for (int64_t i = 0; i < dim; ++i)
+    for (int64_t j = indptr[i]; j < indptr[i + 1]; ++j) {
+      int64_t q = fill[indices[j]]++;
+      t_indices[q] = (int32_t)i;
+      t_data[q] = data[j];
+    }
+  CsrTerm T;
+  T.amp_wf = amp_wf;
+  T.phase_wf = phase_wf;
+  auto up = [&](const void* src, size_t bytes, const void** dst) -> int {
+    void* d = nullptr;
+    CK(cudaMalloc(&d, std::max<size_t>(bytes, 8)));
+    if (bytes) CK(cudaMemcpy(d, src, bytes, cudaMemcpyHostToDevice));
+    p->owned.push_back(d);
+    *dst = d;
+    return 0;
+  };
+  if (up(data, sizeof(double) * nnz, (const void**)&T.data)) return 1;
+  if (up(indices, sizeof(int32_t) * nnz, (const void**)&T.indices)) return 1;
+  if (up(indptr, sizeof(int64_t) * (dim + 1), (const void**)&T.indptr)) return 1;
+  if (up(t_data.data(), sizeof(double) * nnz, (const void**)&T.t_data)) return 1;
+  if (up(t_indices.data(), sizeof(int32_t) * nnz, (const void**)&T.t_indices)) return 1;
+  if (up(t_indptr.data(), sizeof(int64_t) * (dim + 1), (const void**)&T.t_indptr)) return 1;
+  p->csr.push_back(T);
+  if (p->d_csr) cudaFree(p->d_csr);
+  CK(cudaMalloc(&p->d_csr, sizeof(CsrTerm) * p->csr.size()));
+  CK(cudaMemcpy(p->d_csr, p->csr.data(), sizeof(CsrTerm) * p->csr.size(), cudaMemcpyHostToDevice));
+  p->P.csr = p->d_csr;
+  p->P.n_csr = (int)p->csr.size();
+  return 0;
+}
+
+int bqa_apply(bqa_plan* p, const double* record, int64_t record_len, double t, int32_t interaction, int32_t raw,
+              const void* psi_in, void* psi_out, int32_t mem) {
+  if (!p || !record || !psi_in || !psi_out) return fail("bqa_apply: null argument");
+  const int64_t dim = p->P.dim;
+  Staged rec, in, out;
+  if (rec.in(record, sizeof(double) * record_len, BQA_MEM_HOST, p->stream)) return 1;
+  if (in.in(psi_in, sizeof(cplx) * dim, mem, p->stream)) return 1;
+  if (out.out(psi_out, sizeof(cplx) * dim, mem)) return 1;
+  const int diag_id = (int)record[1];
+  const double* V = (diag_id >= 0 && diag_id < (int)p->diags.size()) ? p->diags[diag_id] : nullptr;
+  const cplx* src = (const cplx*)in.dev;
+  Staged rot;
+  if (interaction && V) {  // phi = u psi (SV:347-349)
+    if (rot.out((void*)1, sizeof(cplx) * dim, BQA_MEM_HOST)) return 1;
+    rot.host = nullptr;
+    rotate_kernel<<<grid_for(p, dim, 256), 256, 0, p->stream>>>(dim, V, t, src, (cplx*)rot.dev);
+    LAUNCHED();
+    src = (const cplx*)rot.dev;
+  }
+  const int mode = (raw ? 1 : 0) | (interaction ? 2 : 0);
+  apply_kernel<<<grid_for(p, dim, kApplyThreads), kApplyThreads, 0, p->stream>>>(
+      p->P, (const double*)rec.dev, V, nullptr, t, mode, src, (cplx*)out.dev, nullptr);
+  LAUNCHED();
+  CK(cudaGetLastError());
+  if (out.flush(p->stream)) return 1;
+  CK(cudaStreamSynchronize(p->stream));
+  return 0;
+}
+
+int bqa_norm(bqa_plan* p, const void* psi, int32_t mem, double* norm) {
+  if (!p || !psi || !norm) return fail("bqa_norm: null argument");
+  const int64_t dim = p->P.dim;
+  Staged in;
+  if (in.in(psi, sizeof(cplx) * dim, mem, p->stream)) return 1;
+  const int blocks = grid_for(p, dim, 256, 4);
+  void* sc = nullptr;
+  if (plan_scratch(p, sizeof(double) * (blocks + 1), &sc)) return 1;
+  double* partial = (double*)sc;
+  if (norm2_segments(p, (const cplx*)in.dev, 1, partial, blocks, partial + blocks)) return 1;
+  double n2 = 0.0;
+  CK(cudaMemcpyAsync(&n2, partial + blocks, sizeof(double), cudaMemcpyDeviceToHost, p->stream));
+  CK(cudaStreamSynchronize(p->stream));
+  *norm = sqrt(n2);
+  return 0;
+}
+
+int bqa_normalize(bqa_plan* p, void* psi, int32_t mem) {
+  if (!p || !psi) return fail("bqa_normalize: null argument");
+  const int64_t dim = p->P.dim;
+  Staged buf;
+  if (buf.in(psi, sizeof(cplx) * dim, mem, p->stream)) return 1;
+  if (mem == BQA_MEM_HOST) buf.host = psi;
+  const int blocks = grid_for(p, dim, 256, 4);
+  void* sc = nullptr;
+  if (plan_scratch(p, sizeof(double) * (blocks + 1), &sc)) return 1;
+  double* partial = (double*)sc;
+  if (norm2_segments(p, (const cplx*)buf.dev, 1, partial, blocks, partial + blocks)) return 1;
+  scale_by_norm_kernel<<<dim3(blocks, 1), 256, 0, p->stream>>>((cplx*)buf.dev, dim, dim, partial + blocks);
+  LAUNCHED();
+  CK(cudaGetLastError());
+  if (buf.flush(p->stream)) return 1;
+  CK(cudaStreamSynchronize(p->stream));
+  return 0;
+}
+
+int bqa_expectation(bqa_plan* p, const double* record, int64_t record_len, double t, const void* psi, int32_t mem,
+                    double* average, double* variance) {
+  if (!p || !record || !psi) return fail("bqa_expectation: null argument");
+  const int64_t dim = p->P.dim;
+  Staged rec, in;
+  if (rec.in(record, sizeof(double) * record_len, BQA_MEM_HOST, p->stream)) return 1;
+  if (in.in(psi, sizeof(cplx) * dim, mem, p->stream)) return 1;
+  const int diag_id = (int)record[1];
+  const double* V = (diag_id >= 0 && diag_id < (int)p->diags.size()) ? p->diags[diag_id] : nullptr;
+  const int blocks = grid_for(p, dim, kApplyThreads, 4);
+  void* sc = nullptr;
+  size_t need = sizeof(cplx) * dim + sizeof(double) * (3 * blocks + 3);
+  if (plan_scratch(p, need, &sc)) return 1;
+  cplx* hpsi = (cplx*)sc;
+  double* dots = (double*)(hpsi + dim);
+  apply_kernel<<<blocks, kApplyThreads, 0, p->stream>>>(p->P, (const double*)rec.dev, V, nullptr, t, 1,
+                                                        (const cplx*)in.dev, hpsi, dots);
+  LAUNCHED();
+  finish_sum_kernel<<<1, 256, 0, p->stream>>>(dots, blocks, 3, dots + 3 * blocks);
+  LAUNCHED();
+  CK(cudaGetLastError());
+  double r[3];
+  CK(cudaMemcpyAsync(r, dots + 3 * blocks, sizeof(r), cudaMemcpyDeviceToHost, p->stream));
+  CK(cudaStreamSynchronize(p->stream));
+  if (average) *average = r[0];
+  if (variance) *variance = r[2] - r[0] * r[0];
+  return 0;
+}
+
+int bqa_local_trace(bqa_plan* p, const void* psi, int32_t mem, int32_t n_sites, int32_t site_a, int32_t site_b,
+                    const double* op, double* result) {
+  if (!p || !psi || !op || !result) return fail("bqa_local_trace: null argument");
+  if (n_sites != 1 && n_sites != 2) return fail("bqa_local_trace: n_sites must be 1 or 2");
+  if (site_a < 0 || site_a >= p->P.n_atoms || (n_sites == 2 && (site_b < 0 || site_b >= p->P.n_atoms)))
+    return fail("bqa_local_trace: site out of range");
+  const int64_t dim = p->P.dim;
+  const int m = n_sites == 1 ? p->P.n_level : p->P.n_level * p->P.n_level;
+  Staged in, dop;
+  if (in.in(psi, sizeof(cplx) * dim, mem, p->stream)) return 1;
+  if (dop.in(op, sizeof(cplx) * m * m, BQA_MEM_HOST, p->stream)) return 1;
+  const int blocks = grid_for(p, dim, 256, 4);
+  void* sc = nullptr;
+  if (plan_scratch(p, sizeof(double) * (2 * blocks + 2), &sc)) return 1;
+  double* partial = (double*)sc;
+  local_trace_kernel<<<blocks, 256, 0, p->stream>>>(p->P, (const cplx*)in.dev, n_sites, site_a, site_b,
+                                                    (const cplx*)dop.dev, partial);
+  LAUNCHED();
+  finish_sum_kernel<<<1, 256, 0, p->stream>>>(partial, blocks, 2, partial + 2 * blocks);
+  LAUNCHED();
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(result, partial + 2 * blocks, 2 * sizeof(double), cudaMemcpyDeviceToHost, p->stream));
+  CK(cudaStreamSynchronize(p->stream));
+  return 0;
+}
+
+int bqa_sample(bqa_plan* p, const void* psi, int32_t n_states, const double* uniforms, int32_t n_shots,
+               int32_t project, uint8_t* shots, int32_t mem) {
+  if (!p || !psi || !uniforms || !shots) return fail("bqa_sample: null argument");
+  const int64_t dim = p->P.dim;
+  Staged in, un, out;
+  if (in.in(psi, sizeof(cplx) * dim * n_states, mem, p->stream)) return 1;
+  if (un.in(uniforms, sizeof(double) * (size_t)n_states * n_shots, mem, p->stream)) return 1;
+  if (out.out(shots, (size_t)n_states * n_shots * p->P.n_atoms, mem)) return 1;
+  if (sample_device(p, (const cplx*)in.dev, n_states, (const double*)un.dev, n_shots, project, (uint8_t*)out.dev))
+    return 1;
+  if (out.flush(p->stream)) return 1;
+  CK(cudaStreamSynchronize(p->stream));
+  return 0;
+}
+
+}  // extern "C"
+
+#include "bqa_api_evolve.cuh"

@@ -347,6 +347,14 @@ struct SolverOpts {
   double safety, fac1, fac2, beta;   // scipy: 0.9, dfactor, ifactor, 0.0
   int64_t nmax;      // nsteps
   int nstiff;        // 1000
+  // DOP853 step-size after a REJECTED step.
+  //   0 (default): Hairer's published rule  hnew = h / min(1/fac1, err^(1/8)/safety)  - this is
+  //      SciPy's Fortran dop853.f (<= 1.16; the reference's uv.lock pins 1.15.3).
+  //   1: hnew = h * fac1, which reproduces SciPy 1.18.1's C translation step for step (measured in
+  //      this image: identical nfcn/nstep/naccpt/nrejct, states to 1e-11); it shrinks by the full
+  //      factor fac1 on every rejection and needs ~3.5x more steps on stability-limited problems.
+  //      DOPRI5 is identical in both SciPy generations.
+  int reject_mode;
 };
 
 BQA_HD SolverOpts default_opts(int solver, double atol, double rtol, int64_t nsteps, int interaction) {
@@ -369,6 +377,7 @@ BQA_HD SolverOpts default_opts(int solver, double atol, double rtol, int64_t nst
   }
   o.nmax = nsteps;
   o.nstiff = 1000;
+  o.reject_mode = 0;
   return o;
 }
 
@@ -504,7 +513,10 @@ struct Controller {
       if (reject) hnew = posneg * fmin(fabs(hnew), fabs(h));
       reject = 0;
     } else {
-      hnew = h / fmin(facc1, fac11 / o.safety);
+      if (o.reject_mode == 1 && o.solver != kSolverDopri5)
+        hnew = h / facc1;
+      else
+        hnew = h / fmin(facc1, fac11 / o.safety);
       reject = 1;
       if (naccpt >= 1) nrejct += 1;
       last = 0;

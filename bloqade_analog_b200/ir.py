@@ -381,6 +381,14 @@ def flatten_waveform(wf: Waveform) -> List[Piece]:
                     phi = min(float(h), b)
                     if phi > plo or (plo == -math.inf):
                         pieces.append(Piece(plo, phi, a, scale, c))
+        elif hasattr(node, "pieces"):  # serialize.PieceTable: an already flattened table
+            fshift = float(shift)
+            flo = -math.inf if lo is None else float(lo)
+            for p in node.pieces:
+                plo = max(flo, p.lo + fshift) if p.lo != -math.inf else flo
+                phi = p.hi + fshift if hi is None else min(float(hi), p.hi + fshift)
+                if phi > plo:
+                    pieces.append(Piece(plo, phi, p.offset + fshift, scale * p.scale, p.coeffs))
         elif isinstance(node, Append):
             append_time = Decimal(0)
             first = True

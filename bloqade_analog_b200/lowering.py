@@ -85,13 +85,14 @@ class _WaveformTable:
         self.wf_start: List[int] = [0]
         self.pieces: List[List[float]] = []
         self.coefs: List[float] = []
-        self._ids: Dict[int, int] = {}
+        self._ids: Dict[tuple, int] = {}
 
     def add(self, wf: Waveform) -> int:
-        key = id(wf)
+        flat = flatten_waveform(wf)
+        key = tuple(flat)  # waveforms with identical piece tables share one entry
         if key in self._ids:
             return self._ids[key]
-        for p in flatten_waveform(wf):
+        for p in flat:
             self.pieces.append([p.lo, p.hi, p.offset, p.scale, float(len(self.coefs)), float(len(p.coeffs))])
             self.coefs.extend(p.coeffs)
         self.wf_start.append(len(self.pieces))

@@ -12,8 +12,14 @@ with SciPy's wrapper settings (scipy/integrate/_ode.py: safety 0.9, beta 0.0 - w
 its default 0.04 -, dfactor/ifactor 0.2/10 resp. 0.3/6, max_step = first_step = 0, i.e. automatic
 initial step, and a fresh start on every integrate() call).
 
-Pinning: `tests/test_oracle_dop.py` checks the restatement against SciPy itself (same final state
-to ~1e-13 and identical nfcn / nstep / naccpt / nrejct counters) on the golden programs.
+`reject_mode="hairer"` is the published rule for the step size after a rejected DOP853 step,
+hnew = h / min(1/fac1, err^(1/8)/safety); `reject_mode="scipy118"` is hnew = h*fac1, which is what
+this image's SciPy 1.18.1 C translation does (found by tracing its RHS call times; with it the
+restatement reproduces SciPy's nfcn / nstep / naccpt / nrejct exactly and its states to ~1e-13).
+DOPRI5 follows Hairer in both.
+
+Pinning: `tests/test_oracle_golden.py::test_dop_restatement_matches_scipy` checks the restatement against
+SciPy itself (identical counters, same final state) on golden programs.
 """
 from __future__ import annotations
 
@@ -181,11 +187,9 @@ def integrate(f, x0, y0, xend, solver="dop853", atol=1e-7, rtol=1e-14, nsteps=2*
             reject = False
         else:
             if reject_mode == "hairer" or d5:
-                hnew = h / min(facc1, fac11 / safe)
-            elif reject_mode == "facc1":
-                hnew = h / facc1
+                hnew = h / min(facc1, fac11 / safe)  # Hairer's dop853.f / dopri5.f (SciPy <= 1.16)
             else:
-                hnew = h / max(facc1, fac11 / safe)
+                hnew = h / facc1  # "scipy118": what SciPy 1.18.1's C dop853 does (measured)
             reject = True
             if res.naccpt >= 1:
                 res.nrejct += 1

@@ -87,8 +87,8 @@ void hostsim_apply(int n_atoms, int n_level, int64_t dim, const uint32_t* config
 // {status, nfcn, nstep, naccpt, nrejct, h_last}.  Returns the first non-OK status or 1.
 int hostsim_evolve(int n_atoms, int n_level, int64_t dim, const uint32_t* configs, const int32_t* partners,
                    const double* V, const double* rec, int solver, double atol, double rtol, int64_t nsteps,
-                   int interaction, const double* psi0, const double* times, int n_times, double* y_out,
-                   double* stats) {
+                   int interaction, int reject_mode, const double* psi0, const double* times, int n_times,
+                   double* y_out, double* stats) {
   PlanView P = make_plan(n_atoms, n_level, dim, configs, partners);
   std::vector<cplx> store((size_t)kNumVec * dim);
   cplx* vec[kNumVec];
@@ -101,6 +101,7 @@ int hostsim_evolve(int n_atoms, int n_level, int64_t dim, const uint32_t* config
   w.coefs = &cf;
   HostCtx ctx;
   SolverOpts o = default_opts(solver, atol, rtol, nsteps, interaction);
+  o.reject_mode = reject_mode;
   TaskEvolver<HostCtx> ev(ctx, P, rec, V, w, o);
   double t_cur = 0.0;
   int ret = 1;
