@@ -26,7 +26,7 @@ EXPORTS = [
     "bqa_launch_count", "bqa_plan_create", "bqa_plan_destroy", "bqa_plan_set_stream",
     "bqa_plan_add_diagonal", "bqa_plan_build_rydberg", "bqa_plan_get_diagonal", "bqa_plan_add_csr",
     "bqa_apply", "bqa_evolve_batch", "bqa_run_batch", "bqa_norm", "bqa_normalize", "bqa_expectation",
-    "bqa_local_trace", "bqa_sample",
+    "bqa_local_trace", "bqa_sample", "bqa_plan_enable_timing", "bqa_plan_get_timing",
 ]
 
 
@@ -149,6 +149,15 @@ class Plan:
 
     def set_stream(self, stream: int):
         _check(load().bqa_plan_set_stream(self._h, c_void_p(int(stream))))
+
+    def enable_timing(self, on: bool = True):
+        _check(load().bqa_plan_enable_timing(self._h, c_int32(int(on))))
+
+    def get_timing(self):
+        """(cumulative device ms of the bracketed evolve kernels, number of such launches)"""
+        ms, n = c_double(0.0), c_int64(0)
+        _check(load().bqa_plan_get_timing(self._h, byref(ms), byref(n)))
+        return ms.value, n.value
 
     def add_diagonal(self, v: np.ndarray) -> int:
         v = np.ascontiguousarray(v, dtype=np.float64)

@@ -62,6 +62,11 @@ struct bqa_plan {
   // scratch reused across calls
   void* scratch = nullptr;
   size_t scratch_bytes = 0;
+  // instrumentation (bqa_plan_enable_timing)
+  bool timing = false;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  double evolve_ms = 0.0;
+  int64_t evolve_launches = 0;
 };
 
 static int plan_scratch(bqa_plan* p, size_t bytes, void** out) {
@@ -213,7 +218,28 @@ void bqa_plan_destroy(bqa_plan* p) {
   if (p->d_csr) cudaFree(p->d_csr);
   for (void* q : p->owned) cudaFree(q);
   if (p->scratch) cudaFree(p->scratch);
+  if (p->ev0) cudaEventDestroy(p->ev0);
+  if (p->ev1) cudaEventDestroy(p->ev1);
   delete p;
+}
+
+int bqa_plan_enable_timing(bqa_plan* p, int32_t on) {
+  if (!p) return fail("null plan");
+  if (on && !p->ev0) {
+    CK(cudaEventCreate(&p->ev0));
+    CK(cudaEventCreate(&p->ev1));
+  }
+  p->timing = on != 0;
+  p->evolve_ms = 0.0;
+  p->evolve_launches = 0;
+  return 0;
+}
+
+int bqa_plan_get_timing(bqa_plan* p, double* evolve_kernel_ms, int64_t* evolve_kernel_launches) {
+  if (!p) return fail("null plan");
+  if (evolve_kernel_ms) *evolve_kernel_ms = p->evolve_ms;
+  if (evolve_kernel_launches) *evolve_kernel_launches = p->evolve_launches;
+  return 0;
 }
 
 int bqa_plan_set_stream(bqa_plan* p, void* s) {

@@ -34,10 +34,19 @@ static int launch_small(bqa_plan* p, SmallArgs& A, int n_tasks) {
     CK(cudaMalloc(&gws, sizeof(cplx) * A.gws_stride * grid));
   }
   A.gws = gws;
+  if (p->timing) cudaEventRecord(p->ev0, p->stream);
   kern<<<grid, kThreads, dyn, p->stream>>>(A);
   LAUNCHED();
   cudaError_t e = cudaGetLastError();
+  if (p->timing) cudaEventRecord(p->ev1, p->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+  if (p->timing && e == cudaSuccess) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, p->ev0, p->ev1) == cudaSuccess) {
+      p->evolve_ms += ms;
+      p->evolve_launches += 1;
+    }
+  }
   if (gws) cudaFree(gws);
   if (e != cudaSuccess) return fail("evolve_small_kernel: %s", cudaGetErrorString(e));
   return 0;

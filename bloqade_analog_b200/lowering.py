@@ -87,21 +87,26 @@ class _WaveformTable:
         self.coefs: List[float] = []
         self._ids: Dict[tuple, int] = {}
 
-    def add(self, wf: Waveform) -> int:
+    def add(self, wf: Waveform, dedup: bool = True) -> int:
         flat = flatten_waveform(wf)
         key = tuple(flat)  # waveforms with identical piece tables share one entry
-        if key in self._ids:
+        if dedup and key in self._ids:
             return self._ids[key]
         for p in flat:
             self.pieces.append([p.lo, p.hi, p.offset, p.scale, float(len(self.coefs)), float(len(p.coeffs))])
             self.coefs.extend(p.coeffs)
         self.wf_start.append(len(self.pieces))
-        self._ids[key] = len(self.wf_start) - 2
-        return self._ids[key]
+        wid = len(self.wf_start) - 2
+        if dedup:
+            self._ids[key] = wid
+        return wid
 
 
-def pack_task_record(program: EmulatorProgram, diag_id: int = 0) -> np.ndarray:
-    """Flatten the time-dependent part of one task into the float64 task record."""
+def pack_task_record(program: EmulatorProgram, diag_id: int = 0,
+                     extra_waveforms: Sequence[Waveform] = ()) -> np.ndarray:
+    """Flatten the time-dependent part of one task into the float64 task record.
+    `extra_waveforms` are appended to the waveform table (after the program's own, in order, without
+    de-duplication) for generic CSR terms registered with `bqa_plan_add_csr`."""
     reg = program.register
     n = len(reg)
     if n > MAX_ATOMS:
@@ -129,6 +134,8 @@ def pack_task_record(program: EmulatorProgram, diag_id: int = 0) -> np.ndarray:
             for atom, value in term.operator_data.target_atoms.items():
                 scale[atom] += float(value)
             rabi_rows.append([float(w), float(pw), float(slot)] + scale)
+    for wf in extra_waveforms:
+        table.add(wf, dedup=False)
     header = [
         float(program.duration),
         float(diag_id),

@@ -98,6 +98,12 @@ int bqa_plan_get_diagonal(bqa_plan* plan, int32_t diag_id, double* v_host);
 int bqa_plan_add_csr(bqa_plan* plan, int32_t amp_wf, int32_t phase_wf, int64_t nnz, const double* data,
                      const int32_t* indices, const int64_t* indptr);
 
+/* instrumentation for bench.py: when enabled, the evolve engines bracket their kernels with CUDA events
+ * recorded on the plan's stream; get_timing returns the cumulative device time (ms) and the number of
+ * bracketed kernel launches since timing was (re-)enabled. */
+int bqa_plan_enable_timing(bqa_plan* plan, int32_t on);
+int bqa_plan_get_timing(bqa_plan* plan, double* evolve_kernel_ms, int64_t* evolve_kernel_launches);
+
 /* ---- task record layout (float64 array; integers stored as exact doubles) -----------------------
  * replaces the DetuningOperator / RabiOperator lists (state_vector.py:261-298) and the JITWaveform
  * callables (emulate/ir/emulator.py:65-79):
