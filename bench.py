@@ -274,7 +274,7 @@ def gpu_arm(args):
     uniforms = rs.random_sample((args.tasks, SHOTS))
     lower_s = time.perf_counter() - t0
     dim, n_atoms = plan.dim, plan.n_atoms
-    opts = _lib.make_opts(**SOLVER)
+    opts = _lib.make_opts(**SOLVER, engine=args.engine)
 
     stream = torch.cuda.Stream()
     plan.set_stream(stream.cuda_stream)
@@ -387,7 +387,7 @@ def gpu_arm(args):
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": "configs[2]: 4096-task detuning/duration sweep on a 12-atom chain (D=4096 full space), "
                                "dop853 atol=1e-7 rtol=1e-14, 100 shots/task",
-                   "tasks_per_gpu": args.tasks, "dim": dim, "shots": SHOTS, "parallelism": f"task-sharded x{world}, no collective",
+                   "tasks_per_gpu": args.tasks, "engine": args.engine, "dim": dim, "shots": SHOTS, "parallelism": f"task-sharded x{world}, no collective",
                    "l2": "flushed between timed steps (256 MiB write)", "host_lowering_s": round(lower_s, 3),
                    "failed_tasks": bad, "mean_rhs_per_task": nfcn_total / args.tasks},
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int(blob.nbytes + offsets.nbytes + times.nbytes + uniforms.nbytes),
@@ -414,6 +414,7 @@ def main():
     ap.add_argument("--cpu-tasks", type=int, default=3, help="tasks of the bounded CPU-baseline sample")
     ap.add_argument("--hpsi-atoms", type=int, default=25)
     ap.add_argument("--no-hpsi", action="store_true")
+    ap.add_argument("--engine", default="auto", choices=["auto", "cluster", "cta", "streamed"])
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)

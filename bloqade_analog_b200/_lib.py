@@ -16,7 +16,7 @@ import numpy as np
 MEM_HOST = 1
 MEM_DEVICE = 2
 SOLVERS = {"dopri5": 5, "dop853": 8}
-ENGINES = {"auto": 0, "cta": 1, "streamed": 2}
+ENGINES = {"auto": 0, "cta": 1, "streamed": 2, "cluster": 3}
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbqa_b200.so")
@@ -106,7 +106,7 @@ def _ptr(a) -> c_void_p:
 
 
 def make_opts(solver_name="dop853", atol=1e-7, rtol=1e-14, nsteps=2_147_483_647, interaction_picture=False,
-              reject_mode=0, engine="auto") -> SolverOpts:
+              reject_mode=1, engine="auto") -> SolverOpts:
     if solver_name == "lsoda":
         raise NotImplementedError(
             "solver 'lsoda' has no GPU implementation in the B200 backend (and there is no CPU fallback); "

@@ -57,7 +57,7 @@ def run_programs(
     project_hyperfine: bool = True,
     compile_cache: Optional[CompileCache] = None,
     device: Optional[int] = None,
-    reject_mode: int = 0,
+    reject_mode: int = 1,
     engine: str = "auto",
     uniforms: Optional[np.ndarray] = None,
     raise_on_error: bool = True,
@@ -104,7 +104,7 @@ def evolve_programs(
     interaction_picture: bool = False,
     compile_cache: Optional[CompileCache] = None,
     device: Optional[int] = None,
-    reject_mode: int = 0,
+    reject_mode: int = 1,
     engine: str = "auto",
 ) -> Tuple[List[np.ndarray], np.ndarray]:
     """Final state vectors (host complex128) of every program from |0...0>, batched per space."""

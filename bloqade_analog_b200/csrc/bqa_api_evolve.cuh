@@ -1,6 +1,9 @@
 // bqa_api_evolve.cuh - batched evolution entry points (included from bqa_api_ops.cuh)
 #pragma once
 
+#include <stdlib.h>
+
+#include "bqa_cluster.cuh"
 #include "bqa_large.cuh"
 #include "bqa_large_host.cuh"
 
@@ -52,10 +55,80 @@ static int launch_small(bqa_plan* p, SmallArgs& A, int n_tasks) {
   return 0;
 }
 
+// ---- cluster engine: smallest cluster whose distributed shared memory holds all vectors ---------------
+static bool cluster_fit(const bqa_plan* p, int64_t dim, int n_vec, int* csize, uint32_t* chunk) {
+  cudaFuncAttributes fa;
+  if (cudaFuncGetAttributes(&fa, evolve_cluster_kernel) != cudaSuccess) return false;
+  const int64_t budget = p->smem_optin - (int64_t)fa.sharedSizeBytes - 512;
+  for (int c = 1; c <= kMaxCluster; c *= 2) {
+    int64_t ch = (dim + c - 1) / c;
+    ch = (ch + 31) / 32 * 32;
+    if ((int64_t)n_vec * ch * (int64_t)sizeof(cplx) <= budget) {
+      *csize = c;
+      *chunk = (uint32_t)ch;
+      return true;
+    }
+  }
+  return false;
+}
+
+static int launch_cluster(bqa_plan* p, SmallArgs& A, int n_tasks) {
+  ClusterArgs CA;
+  memset(&CA, 0, sizeof(CA));
+  int csize = 1;
+  uint32_t chunk = 0;
+  if (!cluster_fit(p, A.P.dim, A.n_vec, &csize, &chunk)) return fail("cluster engine: state does not fit in 8 CTAs of shared memory");
+  CA.S = A;
+  CA.csize = csize;
+  CA.chunk = chunk;
+  CA.chunk_shift = -1;
+  for (int b = 0; b < 31; ++b)
+    if ((1u << b) == chunk) CA.chunk_shift = b;
+  int threads = (int)std::min<uint32_t>(512u, std::max<uint32_t>(128u, (chunk / 2 + 31) / 32 * 32));
+  if (const char* e = getenv("BQA_CLUSTER_THREADS")) {
+    int v = atoi(e);
+    if (v >= 32 && v <= 512 && v % 32 == 0) threads = v;
+  }
+  const size_t dyn = (size_t)A.n_vec * chunk * sizeof(cplx);
+  CK(cudaFuncSetAttribute(evolve_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.blockDim = dim3(threads);
+  cfg.dynamicSmemBytes = dyn;
+  cfg.stream = p->stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = csize;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cfg.gridDim = dim3(csize * p->sm_count);  // provisional, for the occupancy query
+  int max_clusters = 0;
+  CK(cudaOccupancyMaxActiveClusters(&max_clusters, evolve_cluster_kernel, &cfg));
+  if (max_clusters < 1) return fail("cluster engine: no cluster of %d CTAs x %zu B fits", csize, dyn);
+  const int n_clusters = std::min(n_tasks, max_clusters);
+  cfg.gridDim = dim3(n_clusters * csize);
+  if (p->timing) cudaEventRecord(p->ev0, p->stream);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, evolve_cluster_kernel, CA);
+  LAUNCHED();
+  if (p->timing) cudaEventRecord(p->ev1, p->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+  if (p->timing && e == cudaSuccess) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, p->ev0, p->ev1) == cudaSuccess) {
+      p->evolve_ms += ms;
+      p->evolve_launches += 1;
+    }
+  }
+  if (e != cudaSuccess) return fail("evolve_cluster_kernel (cluster %d, %d threads, %zu B): %s", csize, threads, dyn, cudaGetErrorString(e));
+  return 0;
+}
+
 // all pointers are device pointers; h_times (host copy) is used for the longest-first ordering
 static int evolve_small_device(bqa_plan* p, const double* d_records, const int64_t* d_offsets, int n_tasks,
                                const bqa_solver_opts* o, const cplx* d_psi0, int psi0_mode, const double* d_times,
-                               const double* h_times, int n_times, cplx* d_out, TaskStats* d_stats) {
+                               const double* h_times, int n_times, cplx* d_out, TaskStats* d_stats, bool use_cluster) {
   SmallArgs A;
   memset(&A, 0, sizeof(A));
   A.P = p->P;
@@ -91,7 +164,9 @@ static int evolve_small_device(bqa_plan* p, const double* d_records, const int64
   A.counter = d_counter;
   const int64_t dim = p->P.dim;
   int rc;
-  if (dim <= 256)
+  if (use_cluster)
+    rc = launch_cluster(p, A, n_tasks);
+  else if (dim <= 256)
     rc = launch_small<128>(p, A, n_tasks);
   else if (dim <= 1024)
     rc = launch_small<256>(p, A, n_tasks);
@@ -114,7 +189,11 @@ static int check_opts(const bqa_solver_opts* o) {
 // pick the engine: the CTA-per-task kernel for batches / small states, the streamed kernels for one
 // large state
 static int pick_engine(const bqa_plan* p, const bqa_solver_opts* o, int n_tasks) {
-  if (o->engine == BQA_ENGINE_CTA_PER_TASK || o->engine == BQA_ENGINE_STREAMED) return o->engine;
+  if (o->engine == BQA_ENGINE_CTA_PER_TASK || o->engine == BQA_ENGINE_STREAMED || o->engine == BQA_ENGINE_CLUSTER)
+    return o->engine;
+  int cs = 0;
+  uint32_t ch = 0;
+  if (cluster_fit(p, p->P.dim, o->solver == BQA_SOLVER_DOPRI5 ? 9 : 12, &cs, &ch)) return BQA_ENGINE_CLUSTER;
   if (p->P.dim <= 8192) return BQA_ENGINE_CTA_PER_TASK;
   if ((int64_t)n_tasks >= p->sm_count && p->P.dim <= 65536) return BQA_ENGINE_CTA_PER_TASK;
   return BQA_ENGINE_STREAMED;
@@ -125,9 +204,9 @@ static int evolve_any_device(bqa_plan* p, const double* d_records, const int64_t
                              const bqa_solver_opts* o, const cplx* d_psi0, int psi0_mode, const double* d_times,
                              const double* h_times, int n_times, cplx* d_out, TaskStats* d_stats) {
   const int engine = pick_engine(p, o, n_tasks);
-  if (engine == BQA_ENGINE_CTA_PER_TASK)
+  if (engine == BQA_ENGINE_CTA_PER_TASK || engine == BQA_ENGINE_CLUSTER)
     return evolve_small_device(p, d_records, d_offsets, n_tasks, o, d_psi0, psi0_mode, d_times, h_times, n_times,
-                               d_out, d_stats);
+                               d_out, d_stats, engine == BQA_ENGINE_CLUSTER);
   return evolve_large_device(p, d_records, h_offsets, h_records, n_tasks, o, d_psi0, psi0_mode, h_times, n_times,
                              d_out, d_stats);
 }

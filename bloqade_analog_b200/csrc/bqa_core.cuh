@@ -210,8 +210,16 @@ BQA_HD void coef_csr_entry(const PlanView& P, const TaskView& tv, double t, int 
 //                  u = exp(-i V t)                                                              (SV:342-359)
 // Returns H-applied value WITHOUT the -i factor when `raw` (used by RydbergHamiltonian._apply, SV:375-398)
 // ------------------------------------------------------------------------------------------------
-template <bool kFull, int kLevel>
-BQA_HD cplx h_apply_element(const PlanView& P, const Coefs& C, const double* V, const cplx* in, int64_t i) {
+// Gather source: `in[p]` for plain (global / CTA-shared) vectors.  Execution contexts whose stage
+// vector is partitioned over the CTAs of a thread-block cluster provide their own accessor with the
+// same operator[] (bqa_cluster.cuh: distributed shared memory).
+struct PtrIn {
+  const cplx* p;
+  BQA_HD cplx operator[](int64_t i) const { return p[i]; }
+};
+
+template <bool kFull, int kLevel, class In>
+BQA_HD cplx h_apply_element(const PlanView& P, const Coefs& C, const double* V, const In& in, int64_t i) {
   const int n = P.n_atoms;
   uint32_t cfg = kFull ? (uint32_t)i : P.configs[i];
   double diag = V ? V[i] : 0.0;
@@ -290,11 +298,17 @@ BQA_HD cplx h_apply_element(const PlanView& P, const Coefs& C, const double* V, 
   return cmake(diag * zi.re + ar, diag * zi.im + ai);
 }
 
-BQA_HD cplx h_apply_dispatch(const PlanView& P, const Coefs& C, const double* V, const cplx* in, int64_t i) {
+template <class In>
+BQA_HD cplx h_apply_dispatch(const PlanView& P, const Coefs& C, const double* V, const In& in, int64_t i) {
   if (P.n_level == 2) {
     return P.full_space ? h_apply_element<true, 2>(P, C, V, in, i) : h_apply_element<false, 2>(P, C, V, in, i);
   }
   return P.full_space ? h_apply_element<true, 3>(P, C, V, in, i) : h_apply_element<false, 3>(P, C, V, in, i);
+}
+BQA_HD cplx h_apply_dispatch(const PlanView& P, const Coefs& C, const double* V, const cplx* in, int64_t i) {
+  PtrIn g;
+  g.p = in;
+  return h_apply_dispatch(P, C, V, g, i);
 }
 
 // u = exp(-i * v * t)

@@ -11,7 +11,12 @@
 //   sync()           barrier + memory visibility inside the context
 //   sum1/2/3(...)    replace each thread's partial by the total over the context (same value and
 //                    same summation order in every thread, so control flow stays uniform)
-//   single(f)        f() executed by exactly one thread, followed by a barrier
+//   single(f)        f() executed by exactly one thread (per CTA), followed by a barrier
+//   for_small(n, f)  like for_each but NOT partitioned over the CTAs of a cluster: every CTA runs all n
+//                    (per-call coefficient tables are replicated in each CTA's shared memory)
+//   sync_local()     barrier that only has to order this CTA's own shared-memory traffic
+//   gather(ptr)      accessor `in[p]` for the stage vector, valid for ANY index p of the state (a
+//                    cluster context resolves indices owned by a peer CTA through DSMEM)
 #pragma once
 #include "bqa_core.cuh"
 
@@ -63,13 +68,13 @@ struct TaskEvolver {
     Coefs* cf = w.coefs;
     const TaskView& tvr = tv;
     const PlanView& Pr = P;
-    ctx.for_each(ne + P.n_csr, [&](int64_t e) {
+    ctx.for_small(ne + P.n_csr, [&](int64_t e) {
       if (e < ne)
         coef_entry(tvr, t, (int)e, *cf);
       else
         coef_csr_entry(Pr, tvr, t, (int)(e - ne), *cf);
     });
-    ctx.sync();
+    ctx.sync_local();
   }
 
   // kout = f(t, .) evaluated on the stage input held in ys (already multiplied by u(t) in the
@@ -78,7 +83,7 @@ struct TaskEvolver {
     eval_coefs(t);
     const PlanView& Pr = P;
     const Coefs& cf = *w.coefs;
-    const cplx* in = ys();
+    const auto in = ctx.gather(ys());
     const double* Vd = V;
     const bool inter = o.interaction != 0;
     ctx.for_each(P.dim, [&](int64_t i) {

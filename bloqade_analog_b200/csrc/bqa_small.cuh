@@ -24,6 +24,16 @@ struct CtaCtx {
     for (int64_t i = threadIdx.x; i < n; i += blockDim.x) f(i);
   }
   __device__ __forceinline__ void sync() { __syncthreads(); }
+  __device__ __forceinline__ void sync_local() { __syncthreads(); }
+  template <class F>
+  __device__ __forceinline__ void for_small(int64_t n, F f) {
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) f(i);
+  }
+  __device__ __forceinline__ PtrIn gather(const cplx* p) const {
+    PtrIn g;
+    g.p = p;
+    return g;
+  }
 
   template <class F>
   __device__ __forceinline__ void single(F f) {

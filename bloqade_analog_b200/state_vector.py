@@ -267,7 +267,7 @@ class AnalogGate:
         times: Union[Sequence[float], np.ndarray] = (),
         interaction_picture: bool = False,
         *,
-        reject_mode: int = 0,
+        reject_mode: int = 1,
         engine: str = "auto",
     ) -> Iterator[StateVector]:
         """Evolve `state` and yield one StateVector per requested time (SV:574-671).  The whole
@@ -297,7 +297,7 @@ class AnalogGate:
         interaction_picture: bool = False,
         project_hyperfine: bool = True,
         *,
-        reject_mode: int = 0,
+        reject_mode: int = 1,
         engine: str = "auto",
     ) -> np.ndarray:
         """zero state -> evolve -> normalise -> sample, fused in one library call (SV:674-699)"""

@@ -41,6 +41,8 @@ extern "C" {
 #define BQA_ENGINE_AUTO 0
 #define BQA_ENGINE_CTA_PER_TASK 1 /* kernel (5): whole integration inside one CTA per task        */
 #define BQA_ENGINE_STREAMED 2     /* kernels (1)+(2): multi-CTA stage kernels, device controller  */
+#define BQA_ENGINE_CLUSTER 3      /* kernel (5): one thread-block cluster per task, all vectors in
+                                     distributed shared memory (AUTO picks it whenever it fits)    */
 
 typedef struct bqa_plan bqa_plan;
 
@@ -61,7 +63,9 @@ typedef struct {
   int32_t interaction_picture; /* state_vector.py:604-641                                            */
   double atol, rtol;
   int64_t nsteps;
-  int32_t reject_mode;         /* 0 = Hairer / SciPy<=1.16 dop853.f, 1 = SciPy 1.18 C translation     */
+  int32_t reject_mode;         /* DOP853 step after a rejection: 1 = SciPy >= 1.17 C translation (the
+                                  Python-side default: same step sequence and failure codes as the
+                                  oracle), 0 = Hairer dop853.f / SciPy <= 1.16 (fewer steps)         */
   int32_t engine;              /* BQA_ENGINE_*                                                       */
 } bqa_solver_opts;
 

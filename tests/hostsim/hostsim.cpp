@@ -21,6 +21,16 @@ struct HostCtx {
     for (int64_t i = 0; i < n; ++i) f(i);
   }
   void sync() {}
+  void sync_local() {}
+  template <class F>
+  void for_small(int64_t n, F f) {
+    for (int64_t i = 0; i < n; ++i) f(i);
+  }
+  PtrIn gather(const cplx* p) const {
+    PtrIn g;
+    g.p = p;
+    return g;
+  }
   void sum1(double&) {}
   void sum2(double&, double&) {}
   void sum3(double&, double&, double&) {}
