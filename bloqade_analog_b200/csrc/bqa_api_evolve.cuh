@@ -3,7 +3,7 @@
 
 #include <stdlib.h>
 
-#include "bqa_cluster.cuh"
+#include "bqa_cluster_fast.cuh"
 #include "bqa_large.cuh"
 #include "bqa_large_host.cuh"
 
@@ -77,19 +77,36 @@ static int launch_cluster(bqa_plan* p, SmallArgs& A, int n_tasks) {
   memset(&CA, 0, sizeof(CA));
   int csize = 1;
   uint32_t chunk = 0;
-  if (!cluster_fit(p, A.P.dim, A.n_vec, &csize, &chunk)) return fail("cluster engine: state does not fit in 8 CTAs of shared memory");
+  // fused DOP853 path (bqa_cluster_fast.cuh): two-level full space, bit-flip terms only, Schroedinger picture
+  bool fast = A.P.full_space && A.P.n_level == 2 && A.P.n_csr == 0 && !A.o.interaction && A.o.solver == kSolverDop853 &&
+              A.P.dim == ((int64_t)1 << A.P.n_atoms) && getenv("BQA_NO_FAST") == nullptr;
+  if (fast) {
+    fast = cluster_fit(p, A.P.dim, A.n_vec + 1, &csize, &chunk) && (int64_t)chunk * csize == A.P.dim && chunk >= 32;
+  }
+  if (!fast && !cluster_fit(p, A.P.dim, A.n_vec, &csize, &chunk))
+    return fail("cluster engine: state does not fit in 8 CTAs of shared memory");
   CA.S = A;
   CA.csize = csize;
   CA.chunk = chunk;
   CA.chunk_shift = -1;
   for (int b = 0; b < 31; ++b)
     if ((1u << b) == chunk) CA.chunk_shift = b;
+  CA.n_alloc = A.n_vec + (fast ? 1 : 0);
+  CA.fastK = 0;
   int threads = (int)std::min<uint32_t>(512u, std::max<uint32_t>(128u, (chunk / 2 + 31) / 32 * 32));
   if (const char* e = getenv("BQA_CLUSTER_THREADS")) {
     int v = atoi(e);
     if (v >= 32 && v <= 512 && v % 32 == 0) threads = v;
   }
-  const size_t dyn = (size_t)A.n_vec * chunk * sizeof(cplx);
+  if (fast) {
+    CA.fastK = chunk >= 512 ? 4 : (chunk >= 128 ? 2 : 1);
+    if (const char* e = getenv("BQA_FAST_K")) {
+      int v = atoi(e);
+      if ((v == 1 || v == 2 || v == 4) && chunk / v >= 32 && chunk / v <= 512) CA.fastK = v;
+    }
+    threads = (int)chunk / CA.fastK;
+  }
+  const size_t dyn = (size_t)CA.n_alloc * chunk * sizeof(cplx);
   CK(cudaFuncSetAttribute(evolve_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));

@@ -151,106 +151,45 @@ struct ClusterArgs {
   int csize;         // CTAs per cluster
   uint32_t chunk;    // rows per CTA
   int chunk_shift;   // log2(chunk) or -1
+  int n_alloc;       // vectors held per CTA (n_vec, +1 for the fast path's second stage-input buffer)
+  int fastK;         // 0: generic TaskEvolver; 1/2/4: Fast853<K> (bqa_cluster_fast.cuh), blockDim.x*K == chunk
 };
 
-__global__ void __launch_bounds__(512, 1) evolve_cluster_kernel(const ClusterArgs CA) {
-  extern __shared__ __align__(16) unsigned char dyn_smem[];
-  __shared__ Coefs s_coefs;
-  __shared__ double s_red[3 * 32];
-  __shared__ double s_part[8];
-  __shared__ cplx* s_vec[kNumVec];
-  __shared__ int s_task;
-  __shared__ double s_rec[kRecSmemDoubles];
+template <int K>
+struct Fast853;
 
-  const SmallArgs& A = CA.S;
-  cg::cluster_group cl = cg::this_cluster();
-  const int csize = CA.csize;
-  const int rank = csize > 1 ? (int)cl.block_rank() : 0;
+// the output-time loop of AnalogGate._apply (state_vector.py:594-602) around any integrator
+template <class Integrator>
+__device__ __forceinline__ void cluster_run_times(Integrator& I, TaskEvolver<ClusterCtx>& ev, const SmallArgs& A, int task,
+                                                  int rank) {
   const int64_t dim = A.P.dim;
-
-  ClusterCtx ctx;
-  ctx.red = s_red;
-  ctx.part = s_part;
-  ctx.parity = 0;
-  ctx.rank = rank;
-  ctx.csize = csize;
-  ctx.chunk = CA.chunk;
-  ctx.chunk_shift = CA.chunk_shift;
-  ctx.lo = (int64_t)rank * CA.chunk;
-  ctx.hi = ctx.lo + CA.chunk < dim ? ctx.lo + CA.chunk : dim;
-  if (ctx.lo > dim) ctx.lo = dim;
-
-  cplx* smem_vecs = reinterpret_cast<cplx*>(dyn_smem);
-
-  for (;;) {
-    // the cluster's rank-0 CTA pulls the next task; the others read it through DSMEM
-    if (rank == 0 && threadIdx.x == 0) s_task = atomicAdd(A.counter, 1);
-    ctx.sync();
-    const int q = csize > 1 ? *cl.map_shared_rank(&s_task, 0) : s_task;
-    ctx.sync();  // everyone has read s_task before rank 0 may overwrite it
-    if (q >= A.n_tasks) break;
-    const int task = A.order ? A.order[q] : q;
-    const double* rec = A.records + A.offsets[task];
-    const int64_t rec_len = A.offsets[task + 1] - A.offsets[task];
-    if (rec_len <= kRecSmemDoubles) {
-      for (int64_t k = threadIdx.x; k < rec_len; k += blockDim.x) s_rec[k] = rec[k];
-      rec = s_rec;
+  double t_cur = 0.0;
+  bool failed = false;
+  for (int k = 0; k < A.n_times; ++k) {
+    const double t_next = A.times[(int64_t)task * A.n_times + k];
+    TaskStats st;
+    st.status = kStatusOk;
+    st.pad = 0;
+    st.nfcn = st.nstep = st.naccpt = st.nrejct = 0;
+    st.h_last = 0.0;
+    st.t_last = t_cur;
+    if (!failed && t_next != t_cur) {
+      I.integrate(t_cur, t_next);
+      st.status = ev.c.status;
+      st.nfcn = ev.c.nfcn;
+      st.nstep = ev.c.nstep;
+      st.naccpt = ev.c.naccpt;
+      st.nrejct = ev.c.nrejct;
+      st.h_last = ev.c.h;
+      st.t_last = ev.c.x;
+      if (ev.c.status != kStatusOk) failed = true;
+      t_cur = t_next;
+    } else if (failed) {
+      st.status = kStatusInconsistent;
     }
-    // vector table: every vector's chunk lives in this CTA's shared memory, pointers pre-offset so
-    // that vec[v][i] addresses global row i for lo <= i < hi
-    if (threadIdx.x == 0) {
-      for (int v = 0; v < A.n_vec; ++v) s_vec[v] = smem_vecs + (int64_t)v * CA.chunk - ctx.lo;
-    }
-    __syncthreads();
-    {
-      cplx* y = s_vec[kVecY];
-      if (A.psi0_mode == 0) {
-        for (int64_t i = ctx.lo + threadIdx.x; i < ctx.hi; i += blockDim.x) y[i] = cmake(i == 0 ? 1.0 : 0.0, 0.0);
-      } else {
-        const cplx* src = A.psi0 + (A.psi0_mode == 2 ? (int64_t)task * dim : 0);
-        for (int64_t i = ctx.lo + threadIdx.x; i < ctx.hi; i += blockDim.x) y[i] = src[i];
-      }
-    }
-    __syncthreads();
-
-    const int diag_id = (int)rec[1];
-    const double* V = (diag_id >= 0 && diag_id < A.n_diags) ? A.diags[diag_id] : nullptr;
-    Workspace w;
-    w.vec = s_vec;
-    w.coefs = &s_coefs;
-    TaskEvolver<ClusterCtx> ev(ctx, A.P, rec, V, w, A.o);
-
-    double t_cur = 0.0;
-    bool failed = false;
-    for (int k = 0; k < A.n_times; ++k) {
-      const double t_next = A.times[(int64_t)task * A.n_times + k];
-      TaskStats st;
-      st.status = kStatusOk;
-      st.pad = 0;
-      st.nfcn = st.nstep = st.naccpt = st.nrejct = 0;
-      st.h_last = 0.0;
-      st.t_last = t_cur;
-      if (!failed && t_next != t_cur) {
-        ev.integrate(t_cur, t_next);
-        st.status = ev.c.status;
-        st.nfcn = ev.c.nfcn;
-        st.nstep = ev.c.nstep;
-        st.naccpt = ev.c.naccpt;
-        st.nrejct = ev.c.nrejct;
-        st.h_last = ev.c.h;
-        st.t_last = ev.c.x;
-        if (ev.c.status != kStatusOk) failed = true;
-        t_cur = t_next;
-      } else if (failed) {
-        st.status = kStatusInconsistent;
-      }
-      if (A.out) ev.emit_state(t_cur, A.out + ((int64_t)task * A.n_times + k) * dim);
-      if (rank == 0 && threadIdx.x == 0 && A.stats) A.stats[(int64_t)task * A.n_times + k] = st;
-    }
-    ctx.sync();
+    if (A.out) ev.emit_state(t_cur, A.out + ((int64_t)task * A.n_times + k) * dim);
+    if (rank == 0 && threadIdx.x == 0 && A.stats) A.stats[(int64_t)task * A.n_times + k] = st;
   }
-  // no CTA may exit while a peer could still read its shared memory
-  ctx.sync();
 }
 
 }  // namespace bqa
