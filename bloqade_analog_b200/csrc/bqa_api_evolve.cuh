@@ -56,14 +56,14 @@ static int launch_small(bqa_plan* p, SmallArgs& A, int n_tasks) {
 }
 
 // ---- cluster engine: smallest cluster whose distributed shared memory holds all vectors ---------------
-static bool cluster_fit(const bqa_plan* p, int64_t dim, int n_vec, int* csize, uint32_t* chunk) {
+static bool cluster_fit(const bqa_plan* p, int64_t dim, int n_vec, int* csize, uint32_t* chunk, int extra_per_row = 0) {
   cudaFuncAttributes fa;
   if (cudaFuncGetAttributes(&fa, evolve_cluster_kernel) != cudaSuccess) return false;
   const int64_t budget = p->smem_optin - (int64_t)fa.sharedSizeBytes - 512;
   for (int c = 1; c <= kMaxCluster; c *= 2) {
     int64_t ch = (dim + c - 1) / c;
     ch = (ch + 31) / 32 * 32;
-    if ((int64_t)n_vec * ch * (int64_t)sizeof(cplx) <= budget) {
+    if ((int64_t)n_vec * ch * (int64_t)sizeof(cplx) + ch * extra_per_row <= budget) {
       *csize = c;
       *chunk = (uint32_t)ch;
       return true;
@@ -81,7 +81,8 @@ static int launch_cluster(bqa_plan* p, SmallArgs& A, int n_tasks) {
   bool fast = A.P.full_space && A.P.n_level == 2 && A.P.n_csr == 0 && !A.o.interaction && A.o.solver == kSolverDop853 &&
               A.P.dim == ((int64_t)1 << A.P.n_atoms) && getenv("BQA_NO_FAST") == nullptr;
   if (fast) {
-    fast = cluster_fit(p, A.P.dim, A.n_vec + 1, &csize, &chunk) && (int64_t)chunk * csize == A.P.dim && chunk >= 32;
+    fast = cluster_fit(p, A.P.dim, A.n_vec + 1, &csize, &chunk, 8) && (int64_t)chunk * csize == A.P.dim &&
+           chunk >= 256 && chunk <= 1024;
   }
   if (!fast && !cluster_fit(p, A.P.dim, A.n_vec, &csize, &chunk))
     return fail("cluster engine: state does not fit in 8 CTAs of shared memory");
@@ -99,14 +100,13 @@ static int launch_cluster(bqa_plan* p, SmallArgs& A, int n_tasks) {
     if (v >= 32 && v <= 512 && v % 32 == 0) threads = v;
   }
   if (fast) {
-    CA.fastK = chunk >= 512 ? 4 : (chunk >= 128 ? 2 : 1);
-    if (const char* e = getenv("BQA_FAST_K")) {
-      int v = atoi(e);
-      if ((v == 1 || v == 2 || v == 4) && chunk / v >= 32 && chunk / v <= 512) CA.fastK = v;
-    }
-    threads = (int)chunk / CA.fastK;
+    // (K elements per thread, T compute threads) instantiated in bqa_cluster_fast.cuh:
+    //   chunk 1024: (2,512) or (4,256); 512: (2,256); 256: (2,128); 128: (1,128);  + one service warp
+    CA.fastK = 2;
+    if (chunk == 1024 && getenv("BQA_FAST_K4") != nullptr) CA.fastK = 4;
+    threads = (int)chunk / CA.fastK + 32;
   }
-  const size_t dyn = (size_t)CA.n_alloc * chunk * sizeof(cplx);
+  const size_t dyn = (size_t)CA.n_alloc * chunk * sizeof(cplx) + (fast ? (size_t)chunk * sizeof(double) : 0);
   CK(cudaFuncSetAttribute(evolve_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));

@@ -155,9 +155,6 @@ struct ClusterArgs {
   int fastK;         // 0: generic TaskEvolver; 1/2/4: Fast853<K> (bqa_cluster_fast.cuh), blockDim.x*K == chunk
 };
 
-template <int K>
-struct Fast853;
-
 // the output-time loop of AnalogGate._apply (state_vector.py:594-602) around any integrator
 template <class Integrator>
 __device__ __forceinline__ void cluster_run_times(Integrator& I, TaskEvolver<ClusterCtx>& ev, const SmallArgs& A, int task,

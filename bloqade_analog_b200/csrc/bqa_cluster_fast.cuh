@@ -1,16 +1,20 @@
 // bqa_cluster_fast.cuh - fused DOP853 stage loop of the cluster engine for the common operator shape:
 // two-level atoms, full 2^n space, bit-flip Rabi terms only (no generic CSR term), Schroedinger picture.
 //
-// Same arithmetic, in the same order, as the generic TaskEvolver (bqa_evolver.cuh / bqa_evolver_steps.cuh)
-// - the K vectors and stage inputs are bitwise identical - but organised for the machine:
-//   * a thread owns K elements l = tid + T*k of its CTA's chunk; flips of the bits that index k are
-//     register moves, flips of the low log2(T) bits are conflict-free LDS.128, flips of the bits above the
-//     chunk are DSMEM loads from the peer CTA (map_shared_rank);
+// Same algorithm as the generic TaskEvolver (bqa_evolver.cuh / bqa_evolver_steps.cuh) - the partner sums and
+// stage combines add their terms in the same order - but organised for the machine:
+//   * T compute threads (compile time) own K elements l = tid + T*k of the CTA's chunk each; flips of the
+//     bits that index k are register moves, flips of the low log2(T) bits are conflict-free LDS.128 with
+//     immediate offsets, flips of the bits above the chunk are DSMEM loads from a peer CTA (the peer's
+//     window address is mapped once per task);
 //   * the RHS of stage s and the stage combine of stage s+1 are ONE pass over the chunk (the fresh K value
-//     never leaves the thread), writing the next stage input into the OTHER of two ys buffers, so a stage
-//     costs one pass + one cluster barrier instead of two of each;
-//   * the coefficients of the next stage time are evaluated by a few threads of the same pass into the
-//     other of two Coefs buffers.
+//     never leaves the thread), writing the next stage input into the OTHER of two ys buffers: a stage
+//     costs one pass + one cluster barrier;
+//   * real drive coefficients (no phase waveform) take a 2-FMA-per-partner variant;
+//   * one extra SERVICE WARP evaluates the waveform coefficients of the NEXT stage time into the other of
+//     two Coefs buffers while the compute warps work, so that latency chain is off the critical path;
+//   * the static diagonal V of the chunk is cached in shared memory, Butcher tables come from the
+//     constant bank.
 // Reference flow replaced: scipy dop853 driving RydbergHamiltonian._ode_complex_kernel
 // (emulate/ir/state_vector.py:323-334,589-599).
 #pragma once
@@ -20,99 +24,154 @@ namespace bqa {
 
 constexpr int kVecYsB = 12;  // 13th vector of the fast path: second stage-input buffer
 
-template <int K>
+// Butcher rows in the constant bank (uniform LDC instead of L1-flushed global loads)
+namespace ctab {
+#undef BQA_TABLE_QUAL
+#define BQA_TABLE_QUAL __constant__ const
+#include "dop_coeffs.h"
+}  // namespace ctab
+
+template <int K, int T>
 struct Fast853 {
+  static constexpr int LT = (T == 512) ? 9 : (T == 256) ? 8 : (T == 128) ? 7 : (T == 64) ? 6 : 5;
+  static constexpr int LK = (K == 4) ? 2 : (K == 2) ? 1 : 0;
+  static_assert((1 << LT) == T, "T must be 32..512, a power of two");
+
   ClusterCtx& ctx;
+  TaskEvolver<ClusterCtx>& ev;  // generic evolver of the same task (prologue of every integrate call)
   const PlanView& P;
   const TaskView& tv;
-  const double* V;      // static diagonal (global memory) or nullptr
-  cplx** vec;           // shared vector table (pre-offset pointers)
+  cplx* sm;             // dynamic shared memory base (vectors, then the V chunk)
+  const double* Vs;     // chunk of the static diagonal in shared memory, or nullptr
+  cplx** vec;           // shared vector table (pre-offset pointers, shared with the generic evolver)
   Coefs* coefs;         // shared [2]
+  int* realflag;        // shared [2]: all drive coefficients of coefs[b] are real
   const SolverOpts& o;
   Controller& c;
-  int T, lt, m, n, tid;
+  int n, tid;
+  bool compute;         // tid < T (the service warp has compute == false)
+  const cplx* peer[3];  // peers' dynamic shared memory base for rank bits 0..2 (DSMEM window)
   int cur;              // which ys buffer holds the current stage input (0: kVecYs, 1: kVecYsB)
   int ccur;             // which Coefs buffer holds the coefficients of the current stage time
 
-  __device__ __forceinline__ cplx* raw(int v) const { return vec[v] + ctx.lo; }
-  __device__ __forceinline__ cplx* ys_raw(int which) const { return raw(which ? kVecYsB : kVecYs); }
+  // element offset of vector v inside `sm`
+  __device__ __forceinline__ int off(int v) const { return (int)((vec[v] + ctx.lo) - sm); }
+  __device__ __forceinline__ int ys_off(int which) const { return off(which ? kVecYsB : kVecYs); }
 
-  // coefficients at time t into buffer `which` (threads 0..ne-1); visible after the next barrier
-  __device__ __forceinline__ void coefs_into(int which, double t) {
-    if (tid < n) coef_entry(tv, t, tid, coefs[which]);
+  __device__ __forceinline__ void init_peers() {
+    peer[0] = peer[1] = peer[2] = sm;
+    if (ctx.csize > 1) {
+      cg::cluster_group cl = cg::this_cluster();
+      for (int rb = 0; (1 << rb) < ctx.csize; ++rb) peer[rb] = cl.map_shared_rank(sm, ctx.rank ^ (1 << rb));
+    }
   }
 
-  // kout[l] = -i H(t) ys  for this thread's K elements; `own` = ys values of those elements
-  __device__ __forceinline__ void rhs_elems(const cplx* ysr, const Coefs& cf, cplx (&kv)[K]) {
+  // kv[k] = (-i H(t) ys)[l_k] for this thread's K elements
+  template <bool kReal>
+  __device__ __forceinline__ void rhs_elems(int yo, const Coefs& cf, cplx (&kv)[K]) {
     cplx own[K];
     double ar[K], ai[K];
+    const cplx* ysl = sm + yo + tid;
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-      own[k] = ysr[tid + T * k];
+      own[k] = ysl[T * k];
       ar[k] = 0.0;
       ai[k] = 0.0;
     }
+    double dlow = 0.0;  // detuning of the set bits among the low (thread-index) bits
     // bits below log2(T): partner in this CTA's shared memory
-    const int nlow = lt < n ? lt : n;
-    for (int b = 0; b < nlow; ++b) {
-      const double cr = cf.c_re[0][b];
-      const double ci = ((tid >> b) & 1) ? cf.c_im[0][b] : -cf.c_im[0][b];
-      const cplx* pp = ysr + (tid ^ (1 << b));
 #pragma unroll
-      for (int k = 0; k < K; ++k) {
-        const cplx z = pp[T * k];
-        ar[k] += cr * z.re - ci * z.im;
-        ai[k] += cr * z.im + ci * z.re;
+    for (int b = 0; b < LT; ++b) {
+      if (b < n) {
+        const double cr = cf.c_re[0][b];
+        const cplx* pp = sm + yo + (tid ^ (1 << b));
+        if ((tid >> b) & 1) dlow += cf.delta[0][b];
+        if (kReal) {
+#pragma unroll
+          for (int k = 0; k < K; ++k) {
+            const cplx z = pp[T * k];
+            ar[k] += cr * z.re;
+            ai[k] += cr * z.im;
+          }
+        } else {
+          const double ci = ((tid >> b) & 1) ? cf.c_im[0][b] : -cf.c_im[0][b];
+#pragma unroll
+          for (int k = 0; k < K; ++k) {
+            const cplx z = pp[T * k];
+            ar[k] += cr * z.re - ci * z.im;
+            ai[k] += cr * z.im + ci * z.re;
+          }
+        }
       }
     }
+    double dk[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) dk[k] = dlow;
     // bits that index k: partner is another register of this thread
 #pragma unroll
-    for (int jb = 0; (1 << jb) < K; ++jb) {
-      const int b = lt + jb;
+    for (int jb = 0; jb < LK; ++jb) {
+      const int b = LT + jb;
       if (b < n) {
-        const double cr = cf.c_re[0][b], cim = cf.c_im[0][b];
+        const double cr = cf.c_re[0][b], cim = kReal ? 0.0 : cf.c_im[0][b], dl = cf.delta[0][b];
 #pragma unroll
         for (int k = 0; k < K; ++k) {
           const cplx z = own[k ^ (1 << jb)];
-          const double ci = ((k >> jb) & 1) ? cim : -cim;
-          ar[k] += cr * z.re - ci * z.im;
-          ai[k] += cr * z.im + ci * z.re;
+          if ((k >> jb) & 1) dk[k] += dl;
+          if (kReal) {
+            ar[k] += cr * z.re;
+            ai[k] += cr * z.im;
+          } else {
+            const double ci = ((k >> jb) & 1) ? cim : -cim;
+            ar[k] += cr * z.re - ci * z.im;
+            ai[k] += cr * z.im + ci * z.re;
+          }
         }
       }
     }
     // bits above the chunk: partner at the same offset in a peer CTA (DSMEM)
-    for (int b = m; b < n; ++b) {
-      const int rb = b - m;
-      const double cr = cf.c_re[0][b];
-      const double ci = ((ctx.rank >> rb) & 1) ? cf.c_im[0][b] : -cf.c_im[0][b];
-      const cplx* pp = cg::this_cluster().map_shared_rank(const_cast<cplx*>(ysr), ctx.rank ^ (1 << rb)) + tid;
 #pragma unroll
-      for (int k = 0; k < K; ++k) {
-        const cplx z = pp[T * k];
-        ar[k] += cr * z.re - ci * z.im;
-        ai[k] += cr * z.im + ci * z.re;
+    for (int rb = 0; rb < 3; ++rb) {
+      const int b = LT + LK + rb;
+      if (b < n) {
+        const double cr = cf.c_re[0][b];
+        const bool up = (ctx.rank >> rb) & 1;
+        const cplx* pp = peer[rb] + yo + tid;
+        const double dl = up ? cf.delta[0][b] : 0.0;
+        cplx z[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) z[k] = pp[T * k];
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+          dk[k] += dl;
+          if (kReal) {
+            ar[k] += cr * z[k].re;
+            ai[k] += cr * z[k].im;
+          } else {
+            const double ci = up ? cf.c_im[0][b] : -cf.c_im[0][b];
+            ar[k] += cr * z[k].re - ci * z[k].im;
+            ai[k] += cr * z[k].im + ci * z[k].re;
+          }
+        }
       }
     }
-    // diagonal: V[i] - sum over set bits of delta (same order as h_apply_element)
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-      const uint32_t i = (uint32_t)ctx.lo + tid + T * k;
-      double diag = V ? V[i] : 0.0;
-      for (int a = 0; a < n; ++a)
-        if ((i >> a) & 1u) diag -= cf.delta[0][a];
-      const cplx hz = cmake(diag * own[k].re + ar[k], diag * own[k].im + ai[k]);
-      kv[k] = times_minus_i(hz);
+      const double diag = (Vs ? Vs[tid + T * k] : 0.0) - dk[k];
+      kv[k] = cmake(diag * own[k].im + ai[k], -(diag * own[k].re + ar[k]));  // -i * (H ys)
     }
   }
 
-  // next stage input  ysn = y + h * sum_j val[j] K[slot[j]]  for this thread's elements
-  __device__ __forceinline__ void combine_elems(double h, int nnz, const int* slot, const double* val, cplx* ysn) {
+  // next stage input  ysn = y + h * (row of the Butcher table . K)  for this thread's elements.
+  // row >= 0: DOP853 a-row; row == -1: the hinit probe  y + h*K[0]
+  __device__ __forceinline__ void combine_elems(double h, int row, int yn) {
     double sr[K], si[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) sr[k] = si[k] = 0.0;
+    const int nnz = row >= 0 ? ctab::DOP853_a_nnz[row] : 1;
     for (int j = 0; j < nnz; ++j) {
-      const cplx* kj = raw(kVecK + slot[j]) + tid;
-      const double v = val[j];
+      const int slot = row >= 0 ? ctab::DOP853_a_slot[row][j] : 0;
+      const double v = row >= 0 ? ctab::DOP853_a_val[row][j] : 1.0;
+      const cplx* kj = sm + off(kVecK + slot) + tid;
 #pragma unroll
       for (int k = 0; k < K; ++k) {
         const cplx z = kj[T * k];
@@ -120,101 +179,67 @@ struct Fast853 {
         si[k] += v * z.im;
       }
     }
-    const cplx* yy = raw(kVecY) + tid;
+    const cplx* yy = sm + off(kVecY) + tid;
+    cplx* out = sm + yn + tid;
 #pragma unroll
     for (int k = 0; k < K; ++k) {
       const cplx y0 = yy[T * k];
-      ysn[tid + T * k] = cmake(y0.re + h * sr[k], y0.im + h * si[k]);
+      out[T * k] = cmake(y0.re + h * sr[k], y0.im + h * si[k]);
     }
   }
 
-  // One fused pass: [K[dst] = f(ys_cur) with coefs[ccur]] ; [ys_other = y + h*row] ; [coefs[other] at t_next]
-  // then the cluster barrier; flips cur / ccur when a new stage input was produced.
-  __device__ __forceinline__ void pass(bool do_rhs, int dst, bool do_combine, double h, int nnz, const int* slot,
-                                       const double* val, bool do_coefs, double t_next) {
-    if (do_coefs) coefs_into(ccur ^ 1, t_next);
-    if (do_rhs) {
-      cplx kv[K];
-      rhs_elems(ys_raw(cur), coefs[ccur], kv);
-      cplx* kd = raw(kVecK + dst) + tid;
-#pragma unroll
-      for (int k = 0; k < K; ++k) kd[T * k] = kv[k];
+  // service warp: coefficient table of time t into buffer b (+ its "all real" flag)
+  __device__ __forceinline__ void service_coefs(int b, double t) {
+    const int a = tid - T;
+    bool im = false;
+    if (a < n) {
+      coef_entry(tv, t, a, coefs[b]);
+      im = coefs[b].c_im[0][a] != 0.0;
     }
-    if (do_combine) combine_elems(h, nnz, slot, val, ys_raw(cur ^ 1));
+    const unsigned any = __ballot_sync(0xffffffffu, im);
+    if (a == 0) realflag[b] = any ? 0 : 1;
+  }
+
+  // One fused pass: [K[dst] = f(ys_cur) with coefs[ccur]] ; [ys_other = y + h*row] by the compute warps,
+  // [coefs[other] at t_next] by the service warp; then the cluster barrier.
+  __device__ __forceinline__ void pass(bool do_rhs, int dst, int row, double h, bool do_coefs, double t_next) {
+    const bool do_combine = row >= -1;
+    if (compute) {
+      if (do_rhs) {
+        const Coefs& cf = coefs[ccur];
+        const bool real = realflag[ccur] != 0;
+        cplx kv[K];
+        if (real)
+          rhs_elems<true>(ys_off(cur), cf, kv);
+        else
+          rhs_elems<false>(ys_off(cur), cf, kv);
+        cplx* kd = sm + off(kVecK + dst) + tid;
+#pragma unroll
+        for (int k = 0; k < K; ++k) kd[T * k] = kv[k];
+      }
+      if (do_combine) combine_elems(h, row, ys_off(cur ^ 1));
+    } else if (do_coefs) {
+      service_coefs(ccur ^ 1, t_next);
+    }
     ctx.sync();
     if (do_combine) cur ^= 1;
     if (do_coefs) ccur ^= 1;
   }
 
-  __device__ void hinit() {
-    const double atol = o.atol, rtol = o.rtol;
-    const cplx* yy = raw(kVecY) + tid;
-    const cplx* f0 = raw(kVecK + 0) + tid;
-    double dnf = 0.0, dny = 0.0;
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-      const cplx y0 = yy[T * k], f = f0[T * k];
-      double sk = atol + rtol * fabs(y0.re);
-      double a = f.re / sk, b = y0.re / sk;
-      dnf += a * a;
-      dny += b * b;
-      sk = atol + rtol * fabs(y0.im);
-      a = f.im / sk;
-      b = y0.im / sk;
-      dnf += a * a;
-      dny += b * b;
-    }
-    ctx.sum2(dnf, dny);
-    const double h0 = c.hinit_first(dnf, dny);
-    const int one_slot[1] = {0};
-    const double one_val[1] = {1.0};
-    pass(false, 0, true, h0, 1, one_slot, one_val, true, c.x + h0);  // ys = y + h0*f0, coefs(x+h0)
-    pass(true, 1, false, 0.0, 0, nullptr, nullptr, false, 0.0);      // K[1] = f(x+h0, ys)
-    const cplx* f1 = raw(kVecK + 1) + tid;
-    double der2 = 0.0;
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-      const cplx y0 = yy[T * k], f = f0[T * k], g = f1[T * k];
-      double sk = atol + rtol * fabs(y0.re);
-      double a = (g.re - f.re) / sk;
-      der2 += a * a;
-      sk = atol + rtol * fabs(y0.im);
-      a = (g.im - f.im) / sk;
-      der2 += a * a;
-    }
-    ctx.sum1(der2);
-    c.hinit_finish(o, h0, dnf, der2);
-  }
-
-  __device__ void step(int& accepted) {
-    const double x = c.x, h = c.h, tn = x + h;
-    const int64_t n_real = 2 * P.dim;
-    // stage-2 input and its coefficients
-    pass(false, 0, true, h, tables::DOP853_a_nnz[0], tables::DOP853_a_slot[0], tables::DOP853_a_val[0], true,
-         x + tables::DOP853_c[1] * h);
-    for (int s = 0; s < 11; ++s) {
-      const int dst = (s == 9) ? 1 : (s == 10) ? 2 : s + 1;
-      const bool more = s < 10;
-      const double t_next = (s + 1 == 10) ? tn : x + tables::DOP853_c[more ? s + 2 : 1] * h;
-      pass(true, dst, more, h, more ? tables::DOP853_a_nnz[s + 1] : 0, more ? tables::DOP853_a_slot[s + 1] : nullptr,
-           more ? tables::DOP853_a_val[s + 1] : nullptr, more, t_next);
-    }
-    c.nfcn += 11;
-    // new solution, error sums, stiffness denominator; ynew -> slot 4 and -> the other ys buffer
-    double err = 0.0, err3 = 0.0, stden = 0.0;
-    {
-      const int bn = tables::DOP853_b_nnz[0], e5n = tables::DOP853_e5_nnz[0], e3n = tables::DOP853_e3_nnz[0];
+  // new solution ynew -> K slot 4 and -> the other ys buffer; error sums; stiffness denominator
+  __device__ __forceinline__ void final_elems(double h, double& err, double& err3, double& stden) {
+      const int bn = ctab::DOP853_b_nnz[0], e5n = ctab::DOP853_e5_nnz[0], e3n = ctab::DOP853_e3_nnz[0];
       const double atol = o.atol, rtol = o.rtol;
-      const cplx* yy = raw(kVecY) + tid;
-      const cplx* old = ys_raw(cur) + tid;
-      cplx* ynew = raw(kVecK + 4) + tid;
-      cplx* ysn = ys_raw(cur ^ 1) + tid;
+      const cplx* yy = sm + off(kVecY) + tid;
+      const cplx* old = sm + ys_off(cur) + tid;
+      cplx* ynew = sm + off(kVecK + 4) + tid;
+      cplx* ysn = sm + ys_off(cur ^ 1) + tid;
       double sr[K], si[K], e5r[K], e5i[K], e3r[K], e3i[K];
 #pragma unroll
       for (int k = 0; k < K; ++k) sr[k] = si[k] = e5r[k] = e5i[k] = e3r[k] = e3i[k] = 0.0;
       for (int j = 0; j < bn; ++j) {
-        const cplx* kj = raw(kVecK + tables::DOP853_b_slot[0][j]) + tid;
-        const double v = tables::DOP853_b_val[0][j];
+        const cplx* kj = sm + off(kVecK + ctab::DOP853_b_slot[0][j]) + tid;
+        const double v = ctab::DOP853_b_val[0][j];
 #pragma unroll
         for (int k = 0; k < K; ++k) {
           const cplx z = kj[T * k];
@@ -223,8 +248,8 @@ struct Fast853 {
         }
       }
       for (int j = 0; j < e5n; ++j) {
-        const cplx* kj = raw(kVecK + tables::DOP853_e5_slot[0][j]) + tid;
-        const double v = tables::DOP853_e5_val[0][j];
+        const cplx* kj = sm + off(kVecK + ctab::DOP853_e5_slot[0][j]) + tid;
+        const double v = ctab::DOP853_e5_val[0][j];
 #pragma unroll
         for (int k = 0; k < K; ++k) {
           const cplx z = kj[T * k];
@@ -233,8 +258,8 @@ struct Fast853 {
         }
       }
       for (int j = 0; j < e3n; ++j) {
-        const cplx* kj = raw(kVecK + tables::DOP853_e3_slot[0][j]) + tid;
-        const double v = tables::DOP853_e3_val[0][j];
+        const cplx* kj = sm + off(kVecK + ctab::DOP853_e3_slot[0][j]) + tid;
+        const double v = ctab::DOP853_e3_val[0][j];
 #pragma unroll
         for (int k = 0; k < K; ++k) {
           const cplx z = kj[T * k];
@@ -262,23 +287,54 @@ struct Fast853 {
         stden += dr * dr + di * di;
         ysn[T * k] = z;
       }
+  }
+
+  // One attempted DOP853 step as 13 fused passes through ONE call site of pass() (code size):
+  //   it = 0      stage-2 input
+  //   it = 1..11  K of stage it+1 from the current stage input, then the next stage input (it <= 10)
+  //   it = 12     new solution + error norm + decision; if accepted, K4 = f(x+h, ynew) (next step's k1)
+  __device__ __forceinline__ void step(int& accepted) {
+    const double x = c.x, h = c.h, tn = x + h;
+    const int64_t n_real = 2 * P.dim;
+    double stden = 0.0;
+    accepted = 0;
+    for (int it = 0; it <= 12; ++it) {
+      int dst = 0, row = -2;
+      bool do_coefs = false;
+      double t_next = 0.0;
+      if (it < 12) {
+        const int s = it - 1;
+        dst = (s == 9) ? 1 : (s == 10) ? 2 : s + 1;
+        if (it <= 10) {
+          row = it;
+          do_coefs = true;
+          t_next = (it == 10) ? tn : x + ctab::DOP853_c[it + 1] * h;
+        }
+      } else {
+        c.nfcn += 11;
+        double err = 0.0, err3 = 0.0;
+        if (compute) final_elems(h, err, err3, stden);
+        ctx.sum3(err, err3, stden);  // contains the barrier that publishes ynew in the other ys buffer
+        cur ^= 1;
+        accepted = c.decide(o, c.err_dop853(err, err3, n_real));
+        if (!accepted) break;
+        dst = 3;  // the coefficients at tn are those of stage 12, still in coefs[ccur]
+      }
+      pass(it > 0, dst, row, h, do_coefs, t_next);
     }
-    ctx.sum3(err, err3, stden);  // contains the cluster barrier that publishes ynew in the other ys buffer
-    cur ^= 1;
-    accepted = c.decide(o, c.err_dop853(err, err3, n_real));
     if (accepted) {
-      // coefficients at tn are the ones of stage 12, still in coefs[ccur]
-      pass(true, 3, false, 0.0, 0, nullptr, nullptr, false, 0.0);  // K4 = f(x+h, ynew): next step's k1
       c.nfcn += 1;
       if (c.stiff_due(o)) {
-        const cplx* k4 = raw(kVecK + 3) + tid;
-        const cplx* k3 = raw(kVecK + 2) + tid;
         double stnum = 0.0;
+        if (compute) {
+          const cplx* k4 = sm + off(kVecK + 3) + tid;
+          const cplx* k3 = sm + off(kVecK + 2) + tid;
 #pragma unroll
-        for (int k = 0; k < K; ++k) {
-          const cplx a = k4[T * k], b = k3[T * k];
-          const double dr = a.re - b.re, di = a.im - b.im;
-          stnum += dr * dr + di * di;
+          for (int k = 0; k < K; ++k) {
+            const cplx a = k4[T * k], b = k3[T * k];
+            const double dr = a.re - b.re, di = a.im - b.im;
+            stnum += dr * dr + di * di;
+          }
         }
         ctx.sum1(stnum);
         c.stiff_update(o, stnum, stden);
@@ -295,20 +351,13 @@ struct Fast853 {
     }
   }
 
-  // one integrate(x0 -> x1) call (fresh start like scipy's ode.integrate)
-  __device__ void integrate(double x0, double x1) {
+  // one integrate(x0 -> x1) call (fresh start like scipy's ode.integrate).  The prologue (k1, automatic
+  // initial step: 2 RHS per call) runs through the generic evolver; the step loop is the fused one.
+  __device__ __forceinline__ void integrate(double x0, double x1) {
     c.begin(o, x0, x1);
-    // ys = y ; coefs(x0)
-    coefs_into(ccur, x0);
-    {
-      const cplx* yy = raw(kVecY) + tid;
-      cplx* yn = ys_raw(cur) + tid;
-#pragma unroll
-      for (int k = 0; k < K; ++k) yn[T * k] = yy[T * k];
-    }
-    ctx.sync();
-    pass(true, 0, false, 0.0, 0, nullptr, nullptr, false, 0.0);  // K[0] = f(x0, y)
-    hinit();
+    ev.stage_input(x0, 0.0, 0, nullptr, nullptr);
+    ev.rhs_from_ys(x0, ev.k(0));
+    ev.hinit();
     while (!c.done) {
       if (!c.step_begin(o)) break;
       int accepted = 0;
@@ -319,9 +368,10 @@ struct Fast853 {
 };
 
 // ---- the kernel: persistent clusters pulling tasks from the work queue ---------------------------------
-__global__ void __launch_bounds__(512, 1) evolve_cluster_kernel(const ClusterArgs CA) {
+__global__ void __launch_bounds__(544, 1) evolve_cluster_kernel(const ClusterArgs CA) {
   extern __shared__ __align__(16) unsigned char dyn_smem[];
   __shared__ Coefs s_coefs[2];
+  __shared__ int s_real[2];
   __shared__ double s_red[3 * 32];
   __shared__ double s_part[8];
   __shared__ cplx* s_vec[kNumVec + 1];
@@ -388,18 +438,25 @@ __global__ void __launch_bounds__(512, 1) evolve_cluster_kernel(const ClusterArg
     if (CA.fastK == 0) {
       cluster_run_times(ev, ev, A, task, rank);
     } else {
-      const int T = blockDim.x;
-      const int lt = 31 - __clz(T);
-      if (CA.fastK == 4) {
-        Fast853<4> fe{ctx, A.P, ev.tv, V, s_vec, s_coefs, ev.o, ev.c, T, lt, lt + 2, A.P.n_atoms, (int)threadIdx.x, 0, 0};
-        cluster_run_times(fe, ev, A, task, rank);
-      } else if (CA.fastK == 2) {
-        Fast853<2> fe{ctx, A.P, ev.tv, V, s_vec, s_coefs, ev.o, ev.c, T, lt, lt + 1, A.P.n_atoms, (int)threadIdx.x, 0, 0};
-        cluster_run_times(fe, ev, A, task, rank);
-      } else {
-        Fast853<1> fe{ctx, A.P, ev.tv, V, s_vec, s_coefs, ev.o, ev.c, T, lt, lt, A.P.n_atoms, (int)threadIdx.x, 0, 0};
-        cluster_run_times(fe, ev, A, task, rank);
-      }
+      // chunk of the static diagonal -> shared memory (behind the vectors)
+      double* Vs = reinterpret_cast<double*>(smem_vecs + (int64_t)CA.n_alloc * CA.chunk);
+      if (V)
+        for (int64_t l = threadIdx.x; l < (int64_t)CA.chunk; l += blockDim.x) Vs[l] = V[ctx.lo + l];
+      __syncthreads();
+      const int T = (int)blockDim.x - 32;
+      const int tid = (int)threadIdx.x;
+#define BQA_FAST_CASE(KK, TT)                                                                               \
+  {                                                                                                         \
+    Fast853<KK, TT> fe{ctx, ev, A.P, ev.tv, smem_vecs, V ? Vs : nullptr, s_vec, s_coefs, s_real, ev.o, ev.c,    \
+                       A.P.n_atoms, tid, tid < TT, {nullptr, nullptr, nullptr}, 0, 0};                      \
+    fe.init_peers();                                                                                        \
+    cluster_run_times(fe, ev, A, task, rank);                                                               \
+  }
+      if (CA.fastK == 2 && T == 512) BQA_FAST_CASE(2, 512)
+      else if (CA.fastK == 4 && T == 256) BQA_FAST_CASE(4, 256)
+      else if (CA.fastK == 2 && T == 256) BQA_FAST_CASE(2, 256)
+      else if (CA.fastK == 2 && T == 128) BQA_FAST_CASE(2, 128)
+#undef BQA_FAST_CASE
     }
     ctx.sync();
   }

@@ -167,11 +167,10 @@ def test_cluster_fast_path_equals_generic_path(name, monkeypatch):
     assert infidelity(fast.data, gen.data) < 1e-12
     assert np.abs(fast.data - gen.data).max() < 1e-5
     assert infidelity(fast.data, c.data["final_dop853"][-1]) < 1e-8
-    for k in (1, 2):
-        monkeypatch.setenv("BQA_FAST_K", str(k))
-        (alt,) = AnalogGate(h).apply(z, engine="cluster")
-        assert infidelity(alt.data, c.data["final_dop853"][-1]) < 1e-8
-    monkeypatch.delenv("BQA_FAST_K")
+    monkeypatch.setenv("BQA_FAST_K4", "1")  # alternative tiling (4 elements per thread) at chunk 1024
+    (alt,) = AnalogGate(h).apply(z, engine="cluster")
+    assert infidelity(alt.data, c.data["final_dop853"][-1]) < 1e-8
+    monkeypatch.delenv("BQA_FAST_K4")
 
 
 def test_cluster_fast_path_multiple_times_and_psi0():
