@@ -3,7 +3,7 @@
 
 #include <stdlib.h>
 
-#include "bqa_cluster_fast.cuh"
+#include "bqa_cluster_launch.h"
 #include "bqa_large.cuh"
 #include "bqa_large_host.cuh"
 
@@ -57,9 +57,9 @@ static int launch_small(bqa_plan* p, SmallArgs& A, int n_tasks) {
 
 // ---- cluster engine: smallest cluster whose distributed shared memory holds all vectors ---------------
 static bool cluster_fit(const bqa_plan* p, int64_t dim, int n_vec, int* csize, uint32_t* chunk, int extra_per_row = 0) {
-  cudaFuncAttributes fa;
-  if (cudaFuncGetAttributes(&fa, evolve_cluster_kernel) != cudaSuccess) return false;
-  const int64_t budget = p->smem_optin - (int64_t)fa.sharedSizeBytes - 512;
+  const size_t stat = cluster_kernel_static_smem();
+  if (stat == (size_t)-1) return false;
+  const int64_t budget = p->smem_optin - (int64_t)stat - 512;
   for (int c = 1; c <= kMaxCluster; c *= 2) {
     int64_t ch = (dim + c - 1) / c;
     ch = (ch + 31) / 32 * 32;
@@ -107,27 +107,12 @@ static int launch_cluster(bqa_plan* p, SmallArgs& A, int n_tasks) {
     threads = (int)chunk / CA.fastK + 32;
   }
   const size_t dyn = (size_t)CA.n_alloc * chunk * sizeof(cplx) + (fast ? (size_t)chunk * sizeof(double) : 0);
-  CK(cudaFuncSetAttribute(evolve_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
-  cudaLaunchConfig_t cfg;
-  memset(&cfg, 0, sizeof(cfg));
-  cfg.blockDim = dim3(threads);
-  cfg.dynamicSmemBytes = dyn;
-  cfg.stream = p->stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = csize;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  cfg.gridDim = dim3(csize * p->sm_count);  // provisional, for the occupancy query
   int max_clusters = 0;
-  CK(cudaOccupancyMaxActiveClusters(&max_clusters, evolve_cluster_kernel, &cfg));
+  CK(cluster_kernel_max_clusters(csize, threads, dyn, p->sm_count, &max_clusters));
   if (max_clusters < 1) return fail("cluster engine: no cluster of %d CTAs x %zu B fits", csize, dyn);
   const int n_clusters = std::min(n_tasks, max_clusters);
-  cfg.gridDim = dim3(n_clusters * csize);
   if (p->timing) cudaEventRecord(p->ev0, p->stream);
-  cudaError_t e = cudaLaunchKernelEx(&cfg, evolve_cluster_kernel, CA);
+  cudaError_t e = cluster_kernel_launch(CA, n_clusters, threads, dyn, p->stream);
   LAUNCHED();
   if (p->timing) cudaEventRecord(p->ev1, p->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);

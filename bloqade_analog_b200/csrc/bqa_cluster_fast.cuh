@@ -31,50 +31,98 @@ namespace ctab {
 #include "dop_coeffs.h"
 }  // namespace ctab
 
+// ---- explicit shared-space accesses (32-bit shared addresses; LDS/STS instead of generic LD/ST) ----------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ cplx lds_c(uint32_t a) {
+  cplx z;
+  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(z.re), "=d"(z.im) : "r"(a) : "memory");
+  return z;
+}
+__device__ __forceinline__ void sts_c(uint32_t a, cplx z) {
+  asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(a), "d"(z.re), "d"(z.im) : "memory");
+}
+__device__ __forceinline__ double lds_d(uint32_t a) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+  return v;
+}
+// peer CTA's shared memory (DSMEM): map a shared address into the cluster window, load from it
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t a, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ cplx ldsc_c(uint32_t a) {
+  cplx z;
+  asm volatile("ld.shared::cluster.v2.f64 {%0, %1}, [%2];" : "=d"(z.re), "=d"(z.im) : "r"(a) : "memory");
+  return z;
+}
+
+// this thread's view of one vector chunk: element l = tid + idx lives at a + 16*idx
+struct SVec {
+  uint32_t a;
+  __device__ __forceinline__ cplx ld(int idx) const { return lds_c(a + 16u * (uint32_t)idx); }
+  __device__ __forceinline__ void st(int idx, cplx z) const { sts_c(a + 16u * (uint32_t)idx, z); }
+};
+
 template <int K, int T>
 struct Fast853 {
   static constexpr int LT = (T == 512) ? 9 : (T == 256) ? 8 : (T == 128) ? 7 : (T == 64) ? 6 : 5;
   static constexpr int LK = (K == 4) ? 2 : (K == 2) ? 1 : 0;
   static_assert((1 << LT) == T, "T must be 32..512, a power of two");
+  static constexpr uint32_t kOffDelta = 0, kOffCre = sizeof(double) * kMaxSlots * kMaxAtoms,
+                            kOffCim = 2 * sizeof(double) * kMaxSlots * kMaxAtoms;
 
   ClusterCtx& ctx;
   TaskEvolver<ClusterCtx>& ev;  // generic evolver of the same task (prologue of every integrate call)
   const PlanView& P;
   const TaskView& tv;
-  cplx* sm;             // dynamic shared memory base (vectors, then the V chunk)
-  const double* Vs;     // chunk of the static diagonal in shared memory, or nullptr
-  cplx** vec;           // shared vector table (pre-offset pointers, shared with the generic evolver)
+  cplx** vec;           // shared vector table (pre-offset generic pointers, used by the generic evolver)
+  uint32_t* addr_gen;   // the u32 address table as a generic pointer (for the swaps)
   Coefs* coefs;         // shared [2]
   int* realflag;        // shared [2]: all drive coefficients of coefs[b] are real
   const SolverOpts& o;
   Controller& c;
   int n, tid;
   bool compute;         // tid < T (the service warp has compute == false)
-  const cplx* peer[3];  // peers' dynamic shared memory base for rank bits 0..2 (DSMEM window)
+  uint32_t sm_base;     // shared address of the dynamic shared memory (vectors, then the V chunk)
+  uint32_t addr_tab;    // shared address of the u32 table: shared address of every vector's chunk
+  uint32_t coef_base;   // shared address of coefs[0]
+  uint32_t vs_addr;     // shared address of the V chunk, 0 = no static diagonal
+  uint32_t peer_base[3];  // cluster-window address of the peers' dynamic shared memory (rank bits 0..2)
   int cur;              // which ys buffer holds the current stage input (0: kVecYs, 1: kVecYsB)
   int ccur;             // which Coefs buffer holds the coefficients of the current stage time
 
-  // element offset of vector v inside `sm`
-  __device__ __forceinline__ int off(int v) const { return (int)((vec[v] + ctx.lo) - sm); }
-  __device__ __forceinline__ int ys_off(int which) const { return off(which ? kVecYsB : kVecYs); }
+  __device__ __forceinline__ uint32_t addr(int v) const { return lds_u(addr_tab + 4u * (uint32_t)v); }
+  __device__ __forceinline__ SVec svec(int v) const {
+    SVec s;
+    s.a = addr(v) + 16u * (uint32_t)tid;
+    return s;
+  }
+  __device__ __forceinline__ int ysv(int which) const { return which ? kVecYsB : kVecYs; }
 
   __device__ __forceinline__ void init_peers() {
-    peer[0] = peer[1] = peer[2] = sm;
-    if (ctx.csize > 1) {
-      cg::cluster_group cl = cg::this_cluster();
-      for (int rb = 0; (1 << rb) < ctx.csize; ++rb) peer[rb] = cl.map_shared_rank(sm, ctx.rank ^ (1 << rb));
-    }
+    peer_base[0] = peer_base[1] = peer_base[2] = sm_base;
+    if (ctx.csize > 1) peer_base[0] = mapa_u32(sm_base, (uint32_t)(ctx.rank ^ 1));
+    if (ctx.csize > 2) peer_base[1] = mapa_u32(sm_base, (uint32_t)(ctx.rank ^ 2));
+    if (ctx.csize > 4) peer_base[2] = mapa_u32(sm_base, (uint32_t)(ctx.rank ^ 4));
   }
 
-  // kv[k] = (-i H(t) ys)[l_k] for this thread's K elements
+  // kv[k] = (-i H(t) ys)[l_k] for this thread's K elements; ya = shared address of the stage input chunk,
+  // cfa = shared address of the coefficient table
   template <bool kReal>
-  __device__ __forceinline__ void rhs_elems(int yo, const Coefs& cf, cplx (&kv)[K]) {
+  __device__ __forceinline__ void rhs_elems(uint32_t ya, uint32_t cfa, cplx (&kv)[K]) {
     cplx own[K];
     double ar[K], ai[K];
-    const cplx* ysl = sm + yo + tid;
+    const uint32_t me = ya + 16u * (uint32_t)tid;
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-      own[k] = ysl[T * k];
+      own[k] = lds_c(me + 16u * T * k);
       ar[k] = 0.0;
       ai[k] = 0.0;
     }
@@ -83,23 +131,26 @@ struct Fast853 {
 #pragma unroll
     for (int b = 0; b < LT; ++b) {
       if (b < n) {
-        const double cr = cf.c_re[0][b];
-        const cplx* pp = sm + yo + (tid ^ (1 << b));
-        if ((tid >> b) & 1) dlow += cf.delta[0][b];
+        const double cr = lds_d(cfa + kOffCre + 8u * b);
+        const uint32_t pp = ya + 16u * (uint32_t)(tid ^ (1 << b));
+        const bool up = (tid >> b) & 1;
+        if (up) dlow += lds_d(cfa + kOffDelta + 8u * b);
+        cplx z[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) z[k] = lds_c(pp + 16u * T * k);
         if (kReal) {
 #pragma unroll
           for (int k = 0; k < K; ++k) {
-            const cplx z = pp[T * k];
-            ar[k] += cr * z.re;
-            ai[k] += cr * z.im;
+            ar[k] += cr * z[k].re;
+            ai[k] += cr * z[k].im;
           }
         } else {
-          const double ci = ((tid >> b) & 1) ? cf.c_im[0][b] : -cf.c_im[0][b];
+          const double cim = lds_d(cfa + kOffCim + 8u * b);
+          const double ci = up ? cim : -cim;
 #pragma unroll
           for (int k = 0; k < K; ++k) {
-            const cplx z = pp[T * k];
-            ar[k] += cr * z.re - ci * z.im;
-            ai[k] += cr * z.im + ci * z.re;
+            ar[k] += cr * z[k].re - ci * z[k].im;
+            ai[k] += cr * z[k].im + ci * z[k].re;
           }
         }
       }
@@ -112,7 +163,8 @@ struct Fast853 {
     for (int jb = 0; jb < LK; ++jb) {
       const int b = LT + jb;
       if (b < n) {
-        const double cr = cf.c_re[0][b], cim = kReal ? 0.0 : cf.c_im[0][b], dl = cf.delta[0][b];
+        const double cr = lds_d(cfa + kOffCre + 8u * b), dl = lds_d(cfa + kOffDelta + 8u * b);
+        const double cim = kReal ? 0.0 : lds_d(cfa + kOffCim + 8u * b);
 #pragma unroll
         for (int k = 0; k < K; ++k) {
           const cplx z = own[k ^ (1 << jb)];
@@ -133,21 +185,26 @@ struct Fast853 {
     for (int rb = 0; rb < 3; ++rb) {
       const int b = LT + LK + rb;
       if (b < n) {
-        const double cr = cf.c_re[0][b];
+        const double cr = lds_d(cfa + kOffCre + 8u * b);
         const bool up = (ctx.rank >> rb) & 1;
-        const cplx* pp = peer[rb] + yo + tid;
-        const double dl = up ? cf.delta[0][b] : 0.0;
+        const uint32_t pp = peer_base[rb] + (me - sm_base);
+        const double dl = up ? lds_d(cfa + kOffDelta + 8u * b) : 0.0;
         cplx z[K];
 #pragma unroll
-        for (int k = 0; k < K; ++k) z[k] = pp[T * k];
+        for (int k = 0; k < K; ++k) z[k] = ldsc_c(pp + 16u * T * k);
+        if (kReal) {
 #pragma unroll
-        for (int k = 0; k < K; ++k) {
-          dk[k] += dl;
-          if (kReal) {
+          for (int k = 0; k < K; ++k) {
+            dk[k] += dl;
             ar[k] += cr * z[k].re;
             ai[k] += cr * z[k].im;
-          } else {
-            const double ci = up ? cf.c_im[0][b] : -cf.c_im[0][b];
+          }
+        } else {
+          const double cim = lds_d(cfa + kOffCim + 8u * b);
+          const double ci = up ? cim : -cim;
+#pragma unroll
+          for (int k = 0; k < K; ++k) {
+            dk[k] += dl;
             ar[k] += cr * z[k].re - ci * z[k].im;
             ai[k] += cr * z[k].im + ci * z[k].re;
           }
@@ -156,14 +213,15 @@ struct Fast853 {
     }
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-      const double diag = (Vs ? Vs[tid + T * k] : 0.0) - dk[k];
+      const double v = vs_addr ? lds_d(vs_addr + 8u * (uint32_t)(tid + T * k)) : 0.0;
+      const double diag = v - dk[k];
       kv[k] = cmake(diag * own[k].im + ai[k], -(diag * own[k].re + ar[k]));  // -i * (H ys)
     }
   }
 
   // next stage input  ysn = y + h * (row of the Butcher table . K)  for this thread's elements.
   // row >= 0: DOP853 a-row; row == -1: the hinit probe  y + h*K[0]
-  __device__ __forceinline__ void combine_elems(double h, int row, int yn) {
+  __device__ __forceinline__ void combine_elems(double h, int row, int yn_vec) {
     double sr[K], si[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) sr[k] = si[k] = 0.0;
@@ -171,20 +229,21 @@ struct Fast853 {
     for (int j = 0; j < nnz; ++j) {
       const int slot = row >= 0 ? ctab::DOP853_a_slot[row][j] : 0;
       const double v = row >= 0 ? ctab::DOP853_a_val[row][j] : 1.0;
-      const cplx* kj = sm + off(kVecK + slot) + tid;
+      const SVec kj = svec(kVecK + slot);
+      cplx z[K];
+#pragma unroll
+      for (int k = 0; k < K; ++k) z[k] = kj.ld(T * k);
 #pragma unroll
       for (int k = 0; k < K; ++k) {
-        const cplx z = kj[T * k];
-        sr[k] += v * z.re;
-        si[k] += v * z.im;
+        sr[k] += v * z[k].re;
+        si[k] += v * z[k].im;
       }
     }
-    const cplx* yy = sm + off(kVecY) + tid;
-    cplx* out = sm + yn + tid;
+    const SVec yy = svec(kVecY), out = svec(yn_vec);
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-      const cplx y0 = yy[T * k];
-      out[T * k] = cmake(y0.re + h * sr[k], y0.im + h * si[k]);
+      const cplx y0 = yy.ld(T * k);
+      out.st(T * k, cmake(y0.re + h * sr[k], y0.im + h * si[k]));
     }
   }
 
@@ -206,18 +265,19 @@ struct Fast853 {
     const bool do_combine = row >= -1;
     if (compute) {
       if (do_rhs) {
-        const Coefs& cf = coefs[ccur];
+        const uint32_t cfa = coef_base + (uint32_t)ccur * (uint32_t)sizeof(Coefs);
         const bool real = realflag[ccur] != 0;
+        const uint32_t ya = addr(ysv(cur));
         cplx kv[K];
         if (real)
-          rhs_elems<true>(ys_off(cur), cf, kv);
+          rhs_elems<true>(ya, cfa, kv);
         else
-          rhs_elems<false>(ys_off(cur), cf, kv);
-        cplx* kd = sm + off(kVecK + dst) + tid;
+          rhs_elems<false>(ya, cfa, kv);
+        const SVec kd = svec(kVecK + dst);
 #pragma unroll
-        for (int k = 0; k < K; ++k) kd[T * k] = kv[k];
+        for (int k = 0; k < K; ++k) kd.st(T * k, kv[k]);
       }
-      if (do_combine) combine_elems(h, row, ys_off(cur ^ 1));
+      if (do_combine) combine_elems(h, row, ysv(cur ^ 1));
     } else if (do_coefs) {
       service_coefs(ccur ^ 1, t_next);
     }
@@ -230,46 +290,43 @@ struct Fast853 {
   __device__ __forceinline__ void final_elems(double h, double& err, double& err3, double& stden) {
       const int bn = ctab::DOP853_b_nnz[0], e5n = ctab::DOP853_e5_nnz[0], e3n = ctab::DOP853_e3_nnz[0];
       const double atol = o.atol, rtol = o.rtol;
-      const cplx* yy = sm + off(kVecY) + tid;
-      const cplx* old = sm + ys_off(cur) + tid;
-      cplx* ynew = sm + off(kVecK + 4) + tid;
-      cplx* ysn = sm + ys_off(cur ^ 1) + tid;
+      const SVec yy = svec(kVecY), old = svec(ysv(cur)), ynew = svec(kVecK + 4), ysn = svec(ysv(cur ^ 1));
       double sr[K], si[K], e5r[K], e5i[K], e3r[K], e3i[K];
 #pragma unroll
       for (int k = 0; k < K; ++k) sr[k] = si[k] = e5r[k] = e5i[k] = e3r[k] = e3i[k] = 0.0;
       for (int j = 0; j < bn; ++j) {
-        const cplx* kj = sm + off(kVecK + ctab::DOP853_b_slot[0][j]) + tid;
+        const SVec kj = svec(kVecK + ctab::DOP853_b_slot[0][j]);
         const double v = ctab::DOP853_b_val[0][j];
 #pragma unroll
         for (int k = 0; k < K; ++k) {
-          const cplx z = kj[T * k];
+          const cplx z = kj.ld(T * k);
           sr[k] += v * z.re;
           si[k] += v * z.im;
         }
       }
       for (int j = 0; j < e5n; ++j) {
-        const cplx* kj = sm + off(kVecK + ctab::DOP853_e5_slot[0][j]) + tid;
+        const SVec kj = svec(kVecK + ctab::DOP853_e5_slot[0][j]);
         const double v = ctab::DOP853_e5_val[0][j];
 #pragma unroll
         for (int k = 0; k < K; ++k) {
-          const cplx z = kj[T * k];
+          const cplx z = kj.ld(T * k);
           e5r[k] += v * z.re;
           e5i[k] += v * z.im;
         }
       }
       for (int j = 0; j < e3n; ++j) {
-        const cplx* kj = sm + off(kVecK + ctab::DOP853_e3_slot[0][j]) + tid;
+        const SVec kj = svec(kVecK + ctab::DOP853_e3_slot[0][j]);
         const double v = ctab::DOP853_e3_val[0][j];
 #pragma unroll
         for (int k = 0; k < K; ++k) {
-          const cplx z = kj[T * k];
+          const cplx z = kj.ld(T * k);
           e3r[k] += v * z.re;
           e3i[k] += v * z.im;
         }
       }
 #pragma unroll
       for (int k = 0; k < K; ++k) {
-        const cplx yo = yy[T * k];
+        const cplx yo = yy.ld(T * k);
         const cplx z = cmake(yo.re + h * sr[k], yo.im + h * si[k]);
         double sk = atol + rtol * fmax(fabs(yo.re), fabs(z.re));
         double q = e5r[k] / sk;
@@ -281,11 +338,11 @@ struct Fast853 {
         err += q * q;
         q = e3i[k] / sk;
         err3 += q * q;
-        ynew[T * k] = z;
-        const cplx o12 = old[T * k];
+        ynew.st(T * k, z);
+        const cplx o12 = old.ld(T * k);
         const double dr = z.re - o12.re, di = z.im - o12.im;
         stden += dr * dr + di * di;
-        ysn[T * k] = z;
+        ysn.st(T * k, z);
       }
   }
 
@@ -327,11 +384,10 @@ struct Fast853 {
       if (c.stiff_due(o)) {
         double stnum = 0.0;
         if (compute) {
-          const cplx* k4 = sm + off(kVecK + 3) + tid;
-          const cplx* k3 = sm + off(kVecK + 2) + tid;
+          const SVec k4 = svec(kVecK + 3), k3 = svec(kVecK + 2);
 #pragma unroll
           for (int k = 0; k < K; ++k) {
-            const cplx a = k4[T * k], b = k3[T * k];
+            const cplx a = k4.ld(T * k), b = k3.ld(T * k);
             const double dr = a.re - b.re, di = a.im - b.im;
             stnum += dr * dr + di * di;
           }
@@ -340,6 +396,7 @@ struct Fast853 {
         c.stiff_update(o, stnum, stden);
       }
       cplx** vv = vec;
+      uint32_t* aa = addr_gen;
       ctx.single([&]() {
         cplx* t0 = vv[kVecK + 0];
         vv[kVecK + 0] = vv[kVecK + 3];
@@ -347,6 +404,12 @@ struct Fast853 {
         t0 = vv[kVecY];
         vv[kVecY] = vv[kVecK + 4];
         vv[kVecK + 4] = t0;
+        uint32_t a0 = aa[kVecK + 0];
+        aa[kVecK + 0] = aa[kVecK + 3];
+        aa[kVecK + 3] = a0;
+        a0 = aa[kVecY];
+        aa[kVecY] = aa[kVecK + 4];
+        aa[kVecK + 4] = a0;
       });
     }
   }
@@ -372,6 +435,7 @@ __global__ void __launch_bounds__(544, 1) evolve_cluster_kernel(const ClusterArg
   extern __shared__ __align__(16) unsigned char dyn_smem[];
   __shared__ Coefs s_coefs[2];
   __shared__ int s_real[2];
+  __shared__ uint32_t s_addr[kNumVec + 1];  // shared address of every vector's chunk (fast path)
   __shared__ double s_red[3 * 32];
   __shared__ double s_part[8];
   __shared__ cplx* s_vec[kNumVec + 1];
@@ -415,7 +479,10 @@ __global__ void __launch_bounds__(544, 1) evolve_cluster_kernel(const ClusterArg
     // vector table: every vector's chunk lives in this CTA's shared memory, pointers pre-offset so
     // that vec[v][i] addresses global row i for lo <= i < hi
     if (threadIdx.x == 0) {
-      for (int v = 0; v < CA.n_alloc; ++v) s_vec[v] = smem_vecs + (int64_t)v * CA.chunk - ctx.lo;
+      for (int v = 0; v < CA.n_alloc; ++v) {
+        s_vec[v] = smem_vecs + (int64_t)v * CA.chunk - ctx.lo;
+        s_addr[v] = smem_u32(smem_vecs + (int64_t)v * CA.chunk);
+      }
     }
     __syncthreads();
     {
@@ -447,8 +514,9 @@ __global__ void __launch_bounds__(544, 1) evolve_cluster_kernel(const ClusterArg
       const int tid = (int)threadIdx.x;
 #define BQA_FAST_CASE(KK, TT)                                                                               \
   {                                                                                                         \
-    Fast853<KK, TT> fe{ctx, ev, A.P, ev.tv, smem_vecs, V ? Vs : nullptr, s_vec, s_coefs, s_real, ev.o, ev.c,    \
-                       A.P.n_atoms, tid, tid < TT, {nullptr, nullptr, nullptr}, 0, 0};                      \
+    Fast853<KK, TT> fe{ctx, ev, A.P, ev.tv, s_vec, s_addr, s_coefs, s_real, ev.o, ev.c, A.P.n_atoms, tid,   \
+                       tid < TT, smem_u32(smem_vecs), smem_u32(s_addr), smem_u32(s_coefs),                  \
+                       V ? smem_u32(Vs) : 0u, {0u, 0u, 0u}, 0, 0};                                          \
     fe.init_peers();                                                                                        \
     cluster_run_times(fe, ev, A, task, rank);                                                               \
   }

@@ -164,7 +164,7 @@ def test_cluster_fast_path_equals_generic_path(name, monkeypatch):
     monkeypatch.setenv("BQA_NO_FAST", "1")
     (gen,) = AnalogGate(h).apply(z, engine="cluster")
     monkeypatch.delenv("BQA_NO_FAST")
-    assert infidelity(fast.data, gen.data) < 1e-12
+    assert infidelity(fast.data, gen.data) < 1e-8  # borderline accept/reject flips allowed, see above
     assert np.abs(fast.data - gen.data).max() < 1e-5
     assert infidelity(fast.data, c.data["final_dop853"][-1]) < 1e-8
     monkeypatch.setenv("BQA_FAST_K4", "1")  # alternative tiling (4 elements per thread) at chunk 1024
