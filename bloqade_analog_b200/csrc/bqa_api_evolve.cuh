@@ -195,7 +195,10 @@ static int pick_engine(const bqa_plan* p, const bqa_solver_opts* o, int n_tasks)
     return o->engine;
   int cs = 0;
   uint32_t ch = 0;
-  if (cluster_fit(p, p->P.dim, o->solver == BQA_SOLVER_DOPRI5 ? 9 : 12, &cs, &ch)) return BQA_ENGINE_CLUSTER;
+  // measured on B200 (profiles/r01_summary.md): with all vectors on chip the cluster engine is 1.5-2.2x faster
+  // than the CTA-per-task kernel while one or two CTAs hold a task (dim <= 2048 for dop853); at 4 CTAs per task
+  // (dim 4096) the DSMEM gathers and cluster barriers cost more than the CTA kernel's L2 traffic (-10 %)
+  if (cluster_fit(p, p->P.dim, o->solver == BQA_SOLVER_DOPRI5 ? 9 : 12, &cs, &ch) && cs <= 2) return BQA_ENGINE_CLUSTER;
   if (p->P.dim <= 8192) return BQA_ENGINE_CTA_PER_TASK;
   if ((int64_t)n_tasks >= p->sm_count && p->P.dim <= 65536) return BQA_ENGINE_CTA_PER_TASK;
   return BQA_ENGINE_STREAMED;

@@ -11,7 +11,8 @@ from bloqade_analog_b200.lowering import concat_records
 engine = sys.argv[1] if len(sys.argv) > 1 else "auto"
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 148
 dur = float(sys.argv[3]) if len(sys.argv) > 3 else 0.5
-progs = [programs.config3_task(4.0 + 0.1 * k, dur) for k in range(n)]
+n_atoms = int(sys.argv[4]) if len(sys.argv) > 4 else 12
+progs = [programs.config3_task(4.0 + 0.1 * k, dur, n_atoms) for k in range(n)]
 cg = RydbergHamiltonianCodeGen(CompileCache())
 hams = [cg.emit(p) for p in progs]
 plan = hams[0].plan
@@ -21,4 +22,4 @@ opts = _lib.make_opts("dop853", 1e-7, 1e-14, engine=engine)
 plan.enable_timing(True)
 out, st = plan.evolve_batch(blob, off, times, opts)
 ms, k = plan.get_timing()
-print(engine, "tasks", n, "kernel ms", ms, "rhs/task", st["nfcn"].mean(), "us per rhs per task-slot", 1e3 * ms / st["nfcn"].mean())
+print(engine, "atoms", n_atoms, "tasks", n, "kernel ms", ms, "rhs/task", st["nfcn"].mean(), "us per rhs per task-slot", 1e3 * ms / st["nfcn"].mean())
