@@ -13,6 +13,7 @@
 
 #include "../../include/bqa_b200.h"
 #include "bqa_kernels.cuh"
+#include "bqa_apply_tiled.cuh"
 #include "bqa_small.cuh"
 
 using namespace bqa;

@@ -45,6 +45,66 @@ static int sample_device(bqa_plan* p, const cplx* d_psi, int n_seg, const double
   return 0;
 }
 
+// Shared-memory-tiled H(t) psi for large two-level full spaces (bqa_apply_tiled.cuh): pass list for n atoms.
+static bool tiled_passes(const bqa_plan* p, int raw, std::vector<TileSpec>& passes) {
+  const PlanView& P = p->P;
+  const int n = P.n_atoms;
+  if (!P.full_space || P.n_level != 2 || P.n_csr != 0 || n <= kTileBits) return false;
+  if (getenv("BQA_NO_TILED")) return false;
+  // k passes cover 13 + 11 (k - 1) tile bits plus one leftover atom each (gathered from global memory)
+  int k = 1;
+  while (kTileBits + (kTileBits - 2) * (k - 1) + k < n) ++k;
+  int extras = std::max(0, n - (kTileBits + (kTileBits - 2) * (k - 1)));  // taken from the top atoms
+  const int n_tiled = n - extras;
+  int next = 0;
+  for (int i = 0; i < k; ++i) {
+    TileSpec s{};
+    if (i == 0) {
+      s.lo_bits = kTileBits;
+      s.hb = kTileBits;
+      s.first = 1;
+      next = kTileBits;
+    } else {
+      // `fresh` new atoms; the high group is widened downwards to at least 4 bits (lo_bits <= 9) over atoms
+      // already done, which p0 then skips
+      const int fresh = std::min(n_tiled - next, kTileBits - 2);
+      const int tb = std::max(fresh, 4);
+      s.lo_bits = kTileBits - tb;
+      s.hb = next + fresh - tb;
+      s.tb = tb;
+      s.p0 = kTileBits - fresh;
+      next += fresh;
+    }
+    if (i < extras) {
+      s.n_x = 1;
+      s.xbit = n - 1 - i;
+    }
+    passes.push_back(s);
+  }
+  passes.back().last = 1;
+  for (auto& s : passes) s.raw = raw;
+  return true;
+}
+
+// out = [-i] H(t) psi by tiled passes; `in` and `out` must not alias.  t from `t_ptr` (device) when not null.
+static int apply_tiled_launch(bqa_plan* p, const std::vector<TileSpec>& passes, const double* d_rec, const double* V,
+                              const double* t_ptr, double t, const cplx* in, cplx* out) {
+  const size_t dyn = kTileDynSmem;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute(apply_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+    attr_set = true;
+  }
+  const int64_t n_tiles = p->P.dim >> kTileBits;
+  const int grid = (int)std::min<int64_t>(n_tiles, p->sm_count);
+  for (const TileSpec& s : passes) {
+    apply_tiled_kernel<<<grid, kTileThreads, dyn, p->stream>>>(p->P, d_rec, V, t_ptr, t, s, in, out);
+    LAUNCHED();
+  }
+  CK(cudaGetLastError());
+  return 0;
+}
+
 extern "C" {
 
 int bqa_plan_add_csr(bqa_plan* p, int32_t amp_wf, int32_t phase_wf, int64_t nnz, const double* data,
@@ -111,9 +171,14 @@ int bqa_apply(bqa_plan* p, const double* record, int64_t record_len, double t, i
     src = (const cplx*)rot.dev;
   }
   const int mode = (raw ? 1 : 0) | (interaction ? 2 : 0);
-  apply_kernel<<<grid_for(p, dim, kApplyThreads), kApplyThreads, 0, p->stream>>>(
-      p->P, (const double*)rec.dev, V, nullptr, t, mode, src, (cplx*)out.dev, nullptr);
-  LAUNCHED();
+  std::vector<TileSpec> passes;
+  if (!interaction && src != (const cplx*)out.dev && tiled_passes(p, raw ? 1 : 0, passes)) {
+    if (apply_tiled_launch(p, passes, (const double*)rec.dev, V, nullptr, t, src, (cplx*)out.dev)) return 1;
+  } else {
+    apply_kernel<<<grid_for(p, dim, kApplyThreads), kApplyThreads, 0, p->stream>>>(
+        p->P, (const double*)rec.dev, V, nullptr, t, mode, src, (cplx*)out.dev, nullptr);
+    LAUNCHED();
+  }
   CK(cudaGetLastError());
   if (out.flush(p->stream)) return 1;
   CK(cudaStreamSynchronize(p->stream));

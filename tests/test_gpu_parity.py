@@ -394,6 +394,44 @@ def test_large_apply_properties(n_atoms):
         assert abs(out_h[i] - ref) <= 1e-12 * max(1.0, abs(ref))
 
 
+@pytest.mark.parametrize("n_atoms", [14, 15, 16, 19, 24, 25, 26, 27])
+def test_tiled_apply_equals_one_pass(n_atoms, monkeypatch):
+    """the shared-memory-tiled H psi (bqa_apply_tiled.cuh: 1, 2 or 3 passes depending on n) against the one-pass
+    gather kernel on the same inputs: per-atom Rabi amplitudes with a phase (complex coefficients) and a local
+    detuning pattern, raw and -i forms.  Only the summation order differs."""
+    import torch
+    from decimal import Decimal
+
+    phase = ir.piecewise_linear([1.0, 3.0], [0.0, 1.1, 2.3])
+    for ph in (phase, None):
+        prog = programs.adiabatic_program(ir.chain_sites(n_atoms, lattice_spacing=5.1), durations=[1.0, 2.0, 1.0],
+                                          local_drive=ph is not None, phase=ph)
+        fields = prog.pulses[ir.LevelCoupling.Rydberg]
+        pattern = {a: Decimal(str(0.1 + 0.07 * ((a * 5) % 11))) for a in range(n_atoms)}
+        fields.detuning.append(ir.DetuningTerm(ir.DetuningOperatorData(pattern), ir.piecewise_linear([4.0], [-3.0, 8.0])))
+        h = RydbergHamiltonianCodeGen().emit(prog)
+        dim = h.space.size
+        g = torch.Generator(device="cuda").manual_seed(n_atoms)
+        psi = torch.randn(dim, 2, dtype=torch.float64, device="cuda", generator=g)
+        psi /= psi.norm()
+        D = _lib.MEM_DEVICE
+        for raw in (True, False):
+            tiled = torch.full_like(psi, float("nan"))
+            plain = torch.full_like(psi, float("nan"))
+            n0 = _lib.launch_count()
+            h.plan.apply(h.record, 1.7, psi.data_ptr(), tiled.data_ptr(), raw=raw, mem=D)
+            n_tiled = _lib.launch_count() - n0
+            monkeypatch.setenv("BQA_NO_TILED", "1")
+            h.plan.apply(h.record, 1.7, psi.data_ptr(), plain.data_ptr(), raw=raw, mem=D)
+            monkeypatch.delenv("BQA_NO_TILED")
+            torch.cuda.synchronize()
+            assert n_tiled == (1 if n_atoms <= 14 else 2 if n_atoms <= 26 else 3)
+            scale = float(plain.abs().max())
+            assert float((tiled - plain).abs().max()) <= 1e-13 * scale
+        del psi, tiled, plain
+        h.plan.close()
+
+
 def test_large_streamed_evolve_norm_and_sharding_free_consistency():
     """2^20 state, short evolution on the streamed engine vs the CTA-free oracle (SciPy), fidelity < 1e-8"""
     from oracle import emulator as oe
