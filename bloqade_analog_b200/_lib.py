@@ -27,6 +27,8 @@ EXPORTS = [
     "bqa_plan_add_diagonal", "bqa_plan_build_rydberg", "bqa_plan_get_diagonal", "bqa_plan_add_csr",
     "bqa_apply", "bqa_evolve_batch", "bqa_run_batch", "bqa_norm", "bqa_normalize", "bqa_expectation",
     "bqa_local_trace", "bqa_sample", "bqa_plan_enable_timing", "bqa_plan_get_timing",
+    "bqa_shard_sync_bytes", "bqa_shard_alloc", "bqa_shard_open", "bqa_shard_close", "bqa_shard_free",
+    "bqa_plan_build_rydberg_shard", "bqa_apply_sharded", "bqa_evolve_sharded",
 ]
 
 
@@ -38,6 +40,12 @@ class SpaceDesc(Structure):
 class SolverOpts(Structure):
     _fields_ = [("solver", c_int32), ("interaction_picture", c_int32), ("atol", c_double), ("rtol", c_double),
                 ("nsteps", c_int64), ("reject_mode", c_int32), ("engine", c_int32)]
+
+
+class ShardDesc(Structure):
+    """bqa_shard_desc (include/bqa_b200.h)"""
+    _fields_ = [("world", c_int32), ("rank", c_int32), ("n_atoms_total", c_int32), ("pad", c_int32),
+                ("ys", c_void_p * 8), ("sync", c_void_p * 8)]
 
 
 class TaskStats(Structure):
@@ -68,6 +76,7 @@ def load():
     lib = ctypes.CDLL(LIB_PATH)
     lib.bqa_last_error.restype = c_char_p
     lib.bqa_launch_count.restype = c_int64
+    lib.bqa_shard_sync_bytes.restype = c_int64
     lib.bqa_plan_destroy.restype = None
     _lib = lib
     return lib
@@ -174,6 +183,33 @@ class Plan:
         _check(load().bqa_plan_build_rydberg(self._h, _ptr(pair), byref(out)))
         self.n_diags += 1
         return out.value
+
+    def build_rydberg_shard(self, pair: np.ndarray, rank: int) -> int:
+        """diagonal of rank `rank`'s shard of a register of pair.shape[0] atoms (this plan = the local atoms)"""
+        pair = np.ascontiguousarray(pair, dtype=np.float64)
+        out = c_int32(-1)
+        _check(load().bqa_plan_build_rydberg_shard(self._h, c_int32(pair.shape[0]), _ptr(pair), c_int32(rank), byref(out)))
+        self.n_diags += 1
+        return out.value
+
+    def apply_sharded(self, record: np.ndarray, t: float, n_atoms_total: int, rank: int, partners, psi_in: int,
+                      psi_out: int, raw: bool = False):
+        """device pointers only; partners[b] = shard of rank ^ (1 << b)"""
+        record = np.ascontiguousarray(record, dtype=np.float64)
+        arr = (c_void_p * len(partners))(*[int(x) for x in partners])
+        _check(load().bqa_apply_sharded(self._h, _ptr(record), c_int64(record.size), c_double(t), c_int32(int(raw)),
+                                        c_int32(n_atoms_total), c_int32(rank), arr, c_void_p(int(psi_in)),
+                                        c_void_p(int(psi_out))))
+
+    def evolve_sharded(self, record: np.ndarray, opts: "SolverOpts", desc: "ShardDesc", times, psi_out: int,
+                       psi0: Optional[int] = None) -> np.ndarray:
+        record = np.ascontiguousarray(record, dtype=np.float64)
+        times = np.ascontiguousarray(times, dtype=np.float64).reshape(-1)
+        stats = np.zeros(times.size, dtype=STATS_DTYPE)
+        _check(load().bqa_evolve_sharded(self._h, _ptr(record), c_int64(record.size), byref(opts), byref(desc),
+                                         c_void_p(psi0), _ptr(times), c_int32(times.size), c_void_p(int(psi_out)),
+                                         _ptr(stats)))
+        return stats
 
     def get_diagonal(self, diag_id: int) -> np.ndarray:
         v = np.empty(self.dim, dtype=np.float64)
@@ -292,3 +328,30 @@ def sample_host(state_vector, configurations, n_atoms, n_level, uniforms, projec
         return plan.sample(state_vector, uniforms, project)[0]
     finally:
         plan.close()
+
+
+# ---- peer-visible device buffers of a sharded state (CUDA IPC) ------------------------------------------------
+def shard_alloc(nbytes: int):
+    """(device pointer, 64-byte IPC handle) of a zero-filled buffer other ranks can map"""
+    ptr = c_void_p()
+    handle = ctypes.create_string_buffer(64)
+    _check(load().bqa_shard_alloc(c_int64(int(nbytes)), byref(ptr), handle))
+    return int(ptr.value), handle.raw
+
+
+def shard_open(handle: bytes) -> int:
+    ptr = c_void_p()
+    _check(load().bqa_shard_open(ctypes.create_string_buffer(handle, 64), byref(ptr)))
+    return int(ptr.value)
+
+
+def shard_close(ptr: int):
+    _check(load().bqa_shard_close(c_void_p(int(ptr))))
+
+
+def shard_free(ptr: int):
+    _check(load().bqa_shard_free(c_void_p(int(ptr))))
+
+
+def shard_sync_bytes() -> int:
+    return int(load().bqa_shard_sync_bytes())

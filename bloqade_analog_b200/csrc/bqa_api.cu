@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -43,6 +44,15 @@ static int fail(const char* fmt, ...) {
   } while (0)
 
 #define LAUNCHED() g_launches.fetch_add(1, std::memory_order_relaxed)
+
+// Entry of a C-ABI function: drop (and, with BQA_DEBUG set, report) a CUDA error left behind by an earlier
+// unchecked call, so that the cudaGetLastError() after this function's own launches speaks about them only.
+static void api_enter(const char* name) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess && getenv("BQA_DEBUG"))
+    fprintf(stderr, "[bqa] stale CUDA error at entry of %s: %s\n", name, cudaGetErrorString(e));
+}
+#define BQA_ENTER() api_enter(__func__)
 
 // ---------------------------------------------------------------------------------------------------
 // plan
@@ -139,6 +149,7 @@ const char* bqa_last_error(void) { return g_err.c_str(); }
 int64_t bqa_launch_count(void) { return g_launches.load(); }
 
 int bqa_device_count(int32_t* count) {
+  BQA_ENTER();
   int c = 0;
   CK(cudaGetDeviceCount(&c));
   *count = c;
@@ -146,11 +157,13 @@ int bqa_device_count(int32_t* count) {
 }
 
 int bqa_set_device(int32_t device) {
+  BQA_ENTER();
   CK(cudaSetDevice(device));
   return 0;
 }
 
 int bqa_device_info(int32_t* sm_count, int64_t* smem_per_block_optin, int64_t* l2_bytes) {
+  BQA_ENTER();
   int dev = 0, v = 0;
   CK(cudaGetDevice(&dev));
   CK(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev));
@@ -163,6 +176,7 @@ int bqa_device_info(int32_t* sm_count, int64_t* smem_per_block_optin, int64_t* l
 }
 
 int bqa_plan_create(const bqa_space_desc* sp, bqa_plan** out) {
+  BQA_ENTER();
   if (!sp || !out) return fail("bqa_plan_create: null argument");
   if (sp->n_level != 2 && sp->n_level != 3) return fail("bqa_plan_create: n_level must be 2 or 3");
   if (sp->n_atoms < 1 || sp->n_atoms > kMaxAtoms) return fail("bqa_plan_create: n_atoms out of range");
@@ -225,6 +239,7 @@ void bqa_plan_destroy(bqa_plan* p) {
 }
 
 int bqa_plan_enable_timing(bqa_plan* p, int32_t on) {
+  BQA_ENTER();
   if (!p) return fail("null plan");
   if (on && !p->ev0) {
     CK(cudaEventCreate(&p->ev0));
@@ -237,6 +252,7 @@ int bqa_plan_enable_timing(bqa_plan* p, int32_t on) {
 }
 
 int bqa_plan_get_timing(bqa_plan* p, double* evolve_kernel_ms, int64_t* evolve_kernel_launches) {
+  BQA_ENTER();
   if (!p) return fail("null plan");
   if (evolve_kernel_ms) *evolve_kernel_ms = p->evolve_ms;
   if (evolve_kernel_launches) *evolve_kernel_launches = p->evolve_launches;
@@ -244,12 +260,14 @@ int bqa_plan_get_timing(bqa_plan* p, double* evolve_kernel_ms, int64_t* evolve_k
 }
 
 int bqa_plan_set_stream(bqa_plan* p, void* s) {
+  BQA_ENTER();
   if (!p) return fail("null plan");
   p->stream = (cudaStream_t)s;
   return 0;
 }
 
 int bqa_plan_add_diagonal(bqa_plan* p, const double* v_host, int32_t* diag_id) {
+  BQA_ENTER();
   if (!p || !v_host) return fail("bqa_plan_add_diagonal: null argument");
   double* d = nullptr;
   CK(cudaMalloc(&d, sizeof(double) * p->P.dim));
@@ -260,6 +278,7 @@ int bqa_plan_add_diagonal(bqa_plan* p, const double* v_host, int32_t* diag_id) {
 }
 
 int bqa_plan_build_rydberg(bqa_plan* p, const double* pair_host, int32_t* diag_id) {
+  BQA_ENTER();
   if (!p || !pair_host) return fail("bqa_plan_build_rydberg: null argument");
   const int n = p->P.n_atoms;
   double *d = nullptr, *d_pair = nullptr;
@@ -278,6 +297,7 @@ int bqa_plan_build_rydberg(bqa_plan* p, const double* pair_host, int32_t* diag_i
 }
 
 int bqa_plan_get_diagonal(bqa_plan* p, int32_t id, double* v_host) {
+  BQA_ENTER();
   if (!p || id < 0 || id >= (int)p->diags.size()) return fail("bqa_plan_get_diagonal: bad id");
   CK(cudaMemcpy(v_host, p->diags[id], sizeof(double) * p->P.dim, cudaMemcpyDeviceToHost));
   return 0;
@@ -286,3 +306,4 @@ int bqa_plan_get_diagonal(bqa_plan* p, int32_t id, double* v_host) {
 }  // extern "C"
 
 #include "bqa_api_ops.cuh"
+#include "bqa_api_shard.cuh"

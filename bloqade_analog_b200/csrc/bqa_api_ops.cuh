@@ -45,17 +45,19 @@ static int sample_device(bqa_plan* p, const cplx* d_psi, int n_seg, const double
   return 0;
 }
 
-// Shared-memory-tiled H(t) psi for large two-level full spaces (bqa_apply_tiled.cuh): pass list for n atoms.
-static bool tiled_passes(const bqa_plan* p, int raw, std::vector<TileSpec>& passes) {
-  const PlanView& P = p->P;
-  const int n = P.n_atoms;
-  if (!P.full_space || P.n_level != 2 || P.n_csr != 0 || n <= kTileBits) return false;
-  if (getenv("BQA_NO_TILED")) return false;
-  // k passes cover 13 + 11 (k - 1) tile bits plus one leftover atom each (gathered from global memory)
-  int k = 1;
-  while (kTileBits + (kTileBits - 2) * (k - 1) + k < n) ++k;
-  int extras = std::max(0, n - (kTileBits + (kTileBits - 2) * (k - 1)));  // taken from the top atoms
-  const int n_tiled = n - extras;
+// Shared-memory-tiled H(t) psi for large two-level full spaces (bqa_apply_tiled.cuh): pass list.
+// n_loc atoms are local to this device; atoms n_loc .. n_total-1 are the rank bits of a sharded state whose
+// partner shards are `partners[b]` (rank ^ (1 << b)); n_total == n_loc when not sharded.
+static bool tiled_plan(int n_loc, int n_total, int64_t rank, const cplx* const* partners, int raw,
+                       std::vector<TileSpec>& passes) {
+  if (n_loc <= kTileBits) return false;
+  const int g = n_total - n_loc;
+  // k passes cover 13 + 11 (k - 1) tile bits plus ONE leftover atom each (partner amplitudes gathered from
+  // global memory: the peer shards first, then the top local atoms)
+  int k = std::max(1, g);
+  while (kTileBits + (kTileBits - 2) * (k - 1) + (k - g) < n_loc) ++k;
+  const int local_extras = std::max(0, n_loc - (kTileBits + (kTileBits - 2) * (k - 1)));
+  const int n_tiled = n_loc - local_extras;
   int next = 0;
   for (int i = 0; i < k; ++i) {
     TileSpec s{};
@@ -75,30 +77,47 @@ static bool tiled_passes(const bqa_plan* p, int raw, std::vector<TileSpec>& pass
       s.p0 = kTileBits - fresh;
       next += fresh;
     }
-    if (i < extras) {
+    if (i < g) {
       s.n_x = 1;
-      s.xbit = n - 1 - i;
+      s.xbit = n_loc + i;
+      s.x_ptr = partners[i];
+    } else if (i - g < local_extras) {
+      s.n_x = 1;
+      s.xbit = n_loc - 1 - (i - g);
     }
+    s.n_total = n_total;
+    s.idx_hi = (long long)(rank << n_loc);
+    s.raw = raw;
     passes.push_back(s);
   }
   passes.back().last = 1;
-  for (auto& s : passes) s.raw = raw;
   return true;
 }
 
-// out = [-i] H(t) psi by tiled passes; `in` and `out` must not alias.  t from `t_ptr` (device) when not null.
-static int apply_tiled_launch(bqa_plan* p, const std::vector<TileSpec>& passes, const double* d_rec, const double* V,
-                              const double* t_ptr, double t, const cplx* in, cplx* out) {
-  const size_t dyn = kTileDynSmem;
+static bool tiled_passes(const bqa_plan* p, int raw, std::vector<TileSpec>& passes) {
+  const PlanView& P = p->P;
+  if (!P.full_space || P.n_level != 2 || P.n_csr != 0) return false;
+  if (getenv("BQA_NO_TILED")) return false;
+  return tiled_plan(P.n_atoms, P.n_atoms, 0, nullptr, raw, passes);
+}
+
+static int tiled_smem_attr() {
   static bool attr_set = false;
   if (!attr_set) {
-    CK(cudaFuncSetAttribute(apply_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+    CK(cudaFuncSetAttribute(apply_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileDynSmem));
     attr_set = true;
   }
+  return 0;
+}
+
+// out = [-i] H(t) psi by tiled passes; `in` and `out` must not alias
+static int apply_tiled_launch(bqa_plan* p, const std::vector<TileSpec>& passes, const double* d_rec, const double* V,
+                              double t, const cplx* in, cplx* out) {
+  if (tiled_smem_attr()) return 1;
   const int64_t n_tiles = p->P.dim >> kTileBits;
   const int grid = (int)std::min<int64_t>(n_tiles, p->sm_count);
   for (const TileSpec& s : passes) {
-    apply_tiled_kernel<<<grid, kTileThreads, dyn, p->stream>>>(p->P, d_rec, V, t_ptr, t, s, in, out);
+    apply_tiled_kernel<<<grid, kTileThreads, kTileDynSmem, p->stream>>>(p->P, d_rec, V, t, s, in, out);
     LAUNCHED();
   }
   CK(cudaGetLastError());
@@ -109,6 +128,7 @@ extern "C" {
 
 int bqa_plan_add_csr(bqa_plan* p, int32_t amp_wf, int32_t phase_wf, int64_t nnz, const double* data,
                      const int32_t* indices, const int64_t* indptr) {
+  BQA_ENTER();
   if (!p || !data || !indices || !indptr) return fail("bqa_plan_add_csr: null argument");
   if (p->csr.size() >= 8) return fail("bqa_plan_add_csr: at most 8 generic terms");
   const int64_t dim = p->P.dim;
@@ -153,6 +173,7 @@ int bqa_plan_add_csr(bqa_plan* p, int32_t amp_wf, int32_t phase_wf, int64_t nnz,
 
 int bqa_apply(bqa_plan* p, const double* record, int64_t record_len, double t, int32_t interaction, int32_t raw,
               const void* psi_in, void* psi_out, int32_t mem) {
+  BQA_ENTER();
   if (!p || !record || !psi_in || !psi_out) return fail("bqa_apply: null argument");
   const int64_t dim = p->P.dim;
   Staged rec, in, out;
@@ -173,7 +194,7 @@ int bqa_apply(bqa_plan* p, const double* record, int64_t record_len, double t, i
   const int mode = (raw ? 1 : 0) | (interaction ? 2 : 0);
   std::vector<TileSpec> passes;
   if (!interaction && src != (const cplx*)out.dev && tiled_passes(p, raw ? 1 : 0, passes)) {
-    if (apply_tiled_launch(p, passes, (const double*)rec.dev, V, nullptr, t, src, (cplx*)out.dev)) return 1;
+    if (apply_tiled_launch(p, passes, (const double*)rec.dev, V, t, src, (cplx*)out.dev)) return 1;
   } else {
     apply_kernel<<<grid_for(p, dim, kApplyThreads), kApplyThreads, 0, p->stream>>>(
         p->P, (const double*)rec.dev, V, nullptr, t, mode, src, (cplx*)out.dev, nullptr);
@@ -186,6 +207,7 @@ int bqa_apply(bqa_plan* p, const double* record, int64_t record_len, double t, i
 }
 
 int bqa_norm(bqa_plan* p, const void* psi, int32_t mem, double* norm) {
+  BQA_ENTER();
   if (!p || !psi || !norm) return fail("bqa_norm: null argument");
   const int64_t dim = p->P.dim;
   Staged in;
@@ -203,6 +225,7 @@ int bqa_norm(bqa_plan* p, const void* psi, int32_t mem, double* norm) {
 }
 
 int bqa_normalize(bqa_plan* p, void* psi, int32_t mem) {
+  BQA_ENTER();
   if (!p || !psi) return fail("bqa_normalize: null argument");
   const int64_t dim = p->P.dim;
   Staged buf;
@@ -223,6 +246,7 @@ int bqa_normalize(bqa_plan* p, void* psi, int32_t mem) {
 
 int bqa_expectation(bqa_plan* p, const double* record, int64_t record_len, double t, const void* psi, int32_t mem,
                     double* average, double* variance) {
+  BQA_ENTER();
   if (!p || !record || !psi) return fail("bqa_expectation: null argument");
   const int64_t dim = p->P.dim;
   Staged rec, in;
@@ -252,6 +276,7 @@ int bqa_expectation(bqa_plan* p, const double* record, int64_t record_len, doubl
 
 int bqa_local_trace(bqa_plan* p, const void* psi, int32_t mem, int32_t n_sites, int32_t site_a, int32_t site_b,
                     const double* op, double* result) {
+  BQA_ENTER();
   if (!p || !psi || !op || !result) return fail("bqa_local_trace: null argument");
   if (n_sites != 1 && n_sites != 2) return fail("bqa_local_trace: n_sites must be 1 or 2");
   if (site_a < 0 || site_a >= p->P.n_atoms || (n_sites == 2 && (site_b < 0 || site_b >= p->P.n_atoms)))
@@ -278,6 +303,7 @@ int bqa_local_trace(bqa_plan* p, const void* psi, int32_t mem, int32_t n_sites, 
 
 int bqa_sample(bqa_plan* p, const void* psi, int32_t n_states, const double* uniforms, int32_t n_shots,
                int32_t project, uint8_t* shots, int32_t mem) {
+  BQA_ENTER();
   if (!p || !psi || !uniforms || !shots) return fail("bqa_sample: null argument");
   const int64_t dim = p->P.dim;
   Staged in, un, out;

@@ -41,6 +41,11 @@ struct TileSpec {
   int first;     // first pass: out = (diag psi + flips); otherwise out += flips
   int last;      // last pass: multiply by -i unless raw
   int raw;
+  // sharded state (bqa_api_shard.cuh): this rank holds the amplitudes whose index bits >= n_atoms(local) equal
+  // idx_hi; a leftover atom above the local ones has its partner amplitudes at x_ptr (the peer rank's shard)
+  int n_total;           // atoms of the whole register (== local atoms when not sharded)
+  long long idx_hi;      // rank << n_local
+  const cplx* x_ptr;     // null: the leftover atom is local (partner = in[i ^ bit])
 };
 
 struct TileShared {
@@ -106,16 +111,17 @@ __device__ __forceinline__ void apply_tiled_body(const int64_t dim, const int n,
       for (int k = kTileSpare; k < kTilePer; ++k) pre[k - kTileSpare] = src[(size_t)k * stride];
     }
     // per-tile constants: detuning of the atoms outside the tile, leftover-atom partner and sign
+    const int64_t gbase = base | (int64_t)S.idx_hi;  // index in the whole register
     double dbase = 0.0;
     if (kFirst) {
       for (int a = kTileBits; a < n; ++a)
-        if ((base >> a) & 1) dbase += sh.cf.delta[0][a];
+        if ((gbase >> a) & 1) dbase += sh.cf.delta[0][a];
     }
-    const cplx* xin = in + (has_x ? (base ^ ((int64_t)1 << xb)) : base) + off0;
+    const cplx* xin = (S.x_ptr ? S.x_ptr + base : in + (has_x ? (base ^ ((int64_t)1 << xb)) : base)) + off0;
     double xr = 0.0, xi = 0.0;
     if (has_x) {
       xr = sh.cf.c_re[0][xb];
-      xi = ((base >> xb) & 1) ? sh.cf.c_im[0][xb] : -sh.cf.c_im[0][xb];
+      xi = ((gbase >> xb) & 1) ? sh.cf.c_im[0][xb] : -sh.cf.c_im[0][xb];
     }
     const double* Vt = V ? V + base + off0 : nullptr;
     cplx* out_t = out + base + off0;
@@ -189,17 +195,16 @@ __device__ __forceinline__ void apply_tiled_body(const int64_t dim, const int n,
   }
 }
 
-// `t_ptr` (device) overrides `t` when not null (streamed engine: the stage time lives in the device controller)
-__global__ void __launch_bounds__(kTileThreads, 1)
-apply_tiled_kernel(const PlanView P, const double* __restrict__ rec, const double* __restrict__ V,
-                   const double* __restrict__ t_ptr, double t, const TileSpec S, const cplx* __restrict__ in,
-                   cplx* __restrict__ out) {
+// One CTA's share of a tiled pass: coefficients at time t, then the tile loop
+__device__ __forceinline__ void apply_tiled_cta(const PlanView& P, const double* __restrict__ rec,
+                                                const double* __restrict__ V, double t, const TileSpec& S,
+                                                const cplx* __restrict__ in, cplx* __restrict__ out) {
   extern __shared__ __align__(16) unsigned char tile_smem[];
   __shared__ TileShared sh;
   __shared__ int s_complex;
-  const int tid = threadIdx.x, n = P.n_atoms;
-  if (t_ptr) t = *t_ptr;
+  const int tid = threadIdx.x;
   const TaskView tv = task_view(rec);
+  const int n = tv.n_atoms;  // whole register (> P.n_atoms for a sharded state)
   if (tid == 0) s_complex = 0;
   __syncthreads();
   for (int e = tid; e < n; e += blockDim.x) {
@@ -239,6 +244,12 @@ apply_tiled_kernel(const PlanView P, const double* __restrict__ rec, const doubl
     else
       apply_tiled_body<true, false>(P.dim, n, V, S, in, out, tile_smem, sh);
   }
+}
+
+__global__ void __launch_bounds__(kTileThreads, 1)
+apply_tiled_kernel(const PlanView P, const double* __restrict__ rec, const double* __restrict__ V, double t,
+                   const TileSpec S, const cplx* __restrict__ in, cplx* __restrict__ out) {
+  apply_tiled_cta(P, rec, V, t, S, in, out);
 }
 
 }  // namespace bqa

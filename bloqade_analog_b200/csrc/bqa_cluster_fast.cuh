@@ -18,6 +18,10 @@
 // Reference flow replaced: scipy dop853 driving RydbergHamiltonian._ode_complex_kernel
 // (emulate/ir/state_vector.py:323-334,589-599).
 #pragma once
+// -DBQA_PHASE_CLOCKS: per-phase clock64 accounting printed by CTAs 0/1 (profiles/r01_summary.md)
+#ifdef BQA_PHASE_CLOCKS
+#include <cstdio>
+#endif
 #include "bqa_cluster.cuh"
 
 namespace bqa {
@@ -97,6 +101,9 @@ struct Fast853 {
   uint32_t peer_base[3];  // cluster-window address of the peers' dynamic shared memory (rank bits 0..2)
   int cur;              // which ys buffer holds the current stage input (0: kVecYs, 1: kVecYsB)
   int ccur;             // which Coefs buffer holds the coefficients of the current stage time
+#ifdef BQA_PHASE_CLOCKS
+  long long pc_work = 0, pc_sync = 0, pc_final = 0, pc_post = 0, pc_passes = 0, pc_steps = 0;
+#endif
 
   __device__ __forceinline__ uint32_t addr(int v) const { return lds_u(addr_tab + 4u * (uint32_t)v); }
   __device__ __forceinline__ SVec svec(int v) const {
@@ -263,6 +270,9 @@ struct Fast853 {
   // [coefs[other] at t_next] by the service warp; then the cluster barrier.
   __device__ __forceinline__ void pass(bool do_rhs, int dst, int row, double h, bool do_coefs, double t_next) {
     const bool do_combine = row >= -1;
+#ifdef BQA_PHASE_CLOCKS
+    const long long pc0 = clock64();
+#endif
     if (compute) {
       if (do_rhs) {
         const uint32_t cfa = coef_base + (uint32_t)ccur * (uint32_t)sizeof(Coefs);
@@ -281,7 +291,15 @@ struct Fast853 {
     } else if (do_coefs) {
       service_coefs(ccur ^ 1, t_next);
     }
+#ifdef BQA_PHASE_CLOCKS
+    const long long pc1 = clock64();
     ctx.sync();
+    pc_work += pc1 - pc0;
+    pc_sync += clock64() - pc1;
+    pc_passes++;
+#else
+    ctx.sync();
+#endif
     if (do_combine) cur ^= 1;
     if (do_coefs) ccur ^= 1;
   }
@@ -368,17 +386,27 @@ struct Fast853 {
           t_next = (it == 10) ? tn : x + ctab::DOP853_c[it + 1] * h;
         }
       } else {
+#ifdef BQA_PHASE_CLOCKS
+        const long long pf0 = clock64();
+#endif
         c.nfcn += 11;
         double err = 0.0, err3 = 0.0;
         if (compute) final_elems(h, err, err3, stden);
         ctx.sum3(err, err3, stden);  // contains the barrier that publishes ynew in the other ys buffer
         cur ^= 1;
         accepted = c.decide(o, c.err_dop853(err, err3, n_real));
+#ifdef BQA_PHASE_CLOCKS
+        pc_final += clock64() - pf0;
+        pc_steps++;
+#endif
         if (!accepted) break;
         dst = 3;  // the coefficients at tn are those of stage 12, still in coefs[ccur]
       }
       pass(it > 0, dst, row, h, do_coefs, t_next);
     }
+#ifdef BQA_PHASE_CLOCKS
+    const long long pp0 = clock64();
+#endif
     if (accepted) {
       c.nfcn += 1;
       if (c.stiff_due(o)) {
@@ -412,21 +440,35 @@ struct Fast853 {
         aa[kVecK + 4] = a0;
       });
     }
+#ifdef BQA_PHASE_CLOCKS
+    pc_post += clock64() - pp0;
+#endif
   }
 
   // one integrate(x0 -> x1) call (fresh start like scipy's ode.integrate).  The prologue (k1, automatic
   // initial step: 2 RHS per call) runs through the generic evolver; the step loop is the fused one.
   __device__ __forceinline__ void integrate(double x0, double x1) {
+#ifdef BQA_PHASE_CLOCKS
+    const long long pi0 = clock64();
+#endif
     c.begin(o, x0, x1);
     ev.stage_input(x0, 0.0, 0, nullptr, nullptr);
     ev.rhs_from_ys(x0, ev.k(0));
     ev.hinit();
+#ifdef BQA_PHASE_CLOCKS
+    const long long pi1 = clock64();
+#endif
     while (!c.done) {
       if (!c.step_begin(o)) break;
       int accepted = 0;
       step(accepted);
       c.step_end(o, accepted);
     }
+#ifdef BQA_PHASE_CLOCKS
+    if (blockIdx.x < 2 && (tid == 0 || tid == T || tid == 33))
+      printf("PHASE blk %d tid %d: total %lld prologue %lld | passes %lld work %lld sync %lld | steps %lld final %lld post %lld\n",
+             (int)blockIdx.x, tid, clock64() - pi0, pi1 - pi0, pc_passes, pc_work, pc_sync, pc_steps, pc_final, pc_post);
+#endif
   }
 };
 

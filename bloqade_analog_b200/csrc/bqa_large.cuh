@@ -7,6 +7,7 @@
 // the whole adaptive step - accept/reject included - is resident on the GPU
 // (reference flow: AnalogGate._apply, state_vector.py:574-602, driving scipy's dop853/dopri5).
 #pragma once
+#include "bqa_apply_tiled.cuh"
 #include "bqa_kernels.cuh"
 
 namespace bqa {
@@ -22,6 +23,12 @@ struct LargeCtrl {
   int need_stnum;
   double h0, dnf;    // hinit scratch
   double stden;
+  // sharded state (bqa_api_shard.cuh): `world` ranks run this same controller on identical sums, so they
+  // take identical decisions.  peer_partial[r] / peer_flag[r] are rank r's partial-sum array and barrier
+  // counter, mapped into this process (CUDA IPC, NVLink peer access); world <= 1: not sharded.
+  int world, rank;
+  double* peer_partial[8];
+  unsigned long long* peer_flag[8];
 };
 
 enum : int { kTimeX = 0, kTimeHinit = 1, kTimeStage = 2, kTimeNew = 3 };
@@ -130,13 +137,55 @@ __device__ __forceinline__ void lg_store3(LargeCtrl* ctl, double a, double b, do
   }
 }
 
+// rank r's per-CTA partial sums (this rank's own array when not sharded); every rank adds them in the same order
+__device__ __forceinline__ const double* lg_partial_of(const LargeCtrl* ctl, int r) {
+  return ctl->world > 1 ? ctl->peer_partial[r] : ctl->partial;
+}
 __device__ __forceinline__ void lg_total3(const LargeCtrl* ctl, double& a, double& b, double& c) {
   a = b = c = 0.0;
-  for (int k = 0; k < ctl->n_blocks; ++k) {
-    a += ctl->partial[k * 3 + 0];
-    b += ctl->partial[k * 3 + 1];
-    c += ctl->partial[k * 3 + 2];
+  const int world = ctl->world > 1 ? ctl->world : 1;
+  for (int r = 0; r < world; ++r) {
+    const volatile double* part = lg_partial_of(ctl, r);
+    for (int k = 0; k < ctl->n_blocks; ++k) {
+      a += part[k * 3 + 0];
+      b += part[k * 3 + 1];
+      c += part[k * 3 + 2];
+    }
   }
+}
+
+// Cross-rank barrier of a sharded run, device initiated: every rank adds 1 to every rank's counter over
+// NVLink, then spins on its own counter.  Writes of the kernels before it (stage input ys, partial sums) are
+// published by the system-scope fence; launched <<<1, 32>>> on the engine's stream.
+__global__ void lg_barrier(LargeCtrl* ctl) {
+  const int world = ctl->world;
+  if (world <= 1) return;
+  __shared__ unsigned long long target;
+  if (threadIdx.x == 0) {
+    // the barrier count lives next to the counter (slot 1, only this rank touches it), so it carries over
+    // from one evolve call to the next without a reset
+    unsigned long long* epoch = ctl->peer_flag[ctl->rank] + 1;
+    *epoch += 1;
+    target = *epoch * (unsigned long long)world;
+  }
+  __syncthreads();
+  __threadfence_system();
+  if ((int)threadIdx.x < world) atomicAdd_system(ctl->peer_flag[threadIdx.x], 1ull);
+  if (threadIdx.x == 0) {
+    const volatile unsigned long long* mine = ctl->peer_flag[ctl->rank];
+    while (*mine < target) __nanosleep(200);
+  }
+  __syncthreads();
+  __threadfence_system();
+}
+
+// K[dst] = f(t, ys) by one shared-memory-tiled pass (two-level full space, Schroedinger picture); the
+// first pass writes K[dst], later passes accumulate into it (bqa_apply_tiled.cuh)
+__global__ void __launch_bounds__(kTileThreads, 1)
+lg_rhs_tiled(LargeCtrl* ctl, const PlanView P, const double* __restrict__ rec, const double* __restrict__ V, int tmode,
+             int s, int dst, int cond, const TileSpec S) {
+  if (!ctl->active || (cond == 1 && !ctl->accepted)) return;
+  apply_tiled_cta(P, rec, V, lg_time(ctl, tmode, s), S, ctl->vec[kVecYs], ctl->vec[kVecK + dst]);
 }
 
 // hinit reductions: phase 0 -> (dnf, dny); phase 1 -> der2 with f1 = K[1]

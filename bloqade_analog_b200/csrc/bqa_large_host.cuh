@@ -2,7 +2,39 @@
 #pragma once
 #include <stddef.h>
 
-static void lg_enqueue_step(bqa_plan* p, LargeCtrl* ctl, const double* rec, const double* V, bool d5, int gs, int ga) {
+// how the RHS of the streamed engine is launched: gather kernel or tiled passes; sharded or not
+struct LgRhsPlan {
+  bool tiled = false;
+  std::vector<TileSpec> passes;
+  int world = 1;
+  int tile_grid = 1;
+};
+
+static void lg_sync_ranks(bqa_plan* p, LargeCtrl* ctl, const LgRhsPlan& R) {
+  if (R.world <= 1) return;
+  lg_barrier<<<1, 32, 0, p->stream>>>(ctl);
+  LAUNCHED();
+}
+
+// K[dst] = f(t, ys); sharded: a barrier before (ys complete on every rank) and after (peers done reading it)
+static void lg_launch_rhs(bqa_plan* p, LargeCtrl* ctl, const double* rec, const double* V, const LgRhsPlan& R, int ga,
+                          int tmode, int st, int dst, int cond) {
+  cudaStream_t s = p->stream;
+  lg_sync_ranks(p, ctl, R);
+  if (R.tiled) {
+    for (const TileSpec& S : R.passes) {
+      lg_rhs_tiled<<<R.tile_grid, kTileThreads, kTileDynSmem, s>>>(ctl, p->P, rec, V, tmode, st, dst, cond, S);
+      LAUNCHED();
+    }
+  } else {
+    lg_rhs<<<ga, kApplyThreads, 0, s>>>(ctl, p->P, rec, V, tmode, st, dst, cond);
+    LAUNCHED();
+  }
+  lg_sync_ranks(p, ctl, R);
+}
+
+static void lg_enqueue_step(bqa_plan* p, LargeCtrl* ctl, const double* rec, const double* V, bool d5, int gs, int ga,
+                            const LgRhsPlan& R, int64_t dim_total) {
   const int64_t dim = p->P.dim;
   cudaStream_t s = p->stream;
   lg_ctl_step_begin<<<1, 1, 0, s>>>(ctl);
@@ -10,36 +42,55 @@ static void lg_enqueue_step(bqa_plan* p, LargeCtrl* ctl, const double* rec, cons
   if (d5) {
     for (int st = 0; st < 5; ++st) {
       lg_combine<<<gs, kLgThreads, 0, s>>>(ctl, dim, V, kTimeStage, st);
-      lg_rhs<<<ga, kApplyThreads, 0, s>>>(ctl, p->P, rec, V, kTimeStage, st, st + 1, 0);
       LAUNCHED();
-      LAUNCHED();
+      lg_launch_rhs(p, ctl, rec, V, R, ga, kTimeStage, st, st + 1, 0);
     }
     lg_final5a<<<gs, kLgThreads, 0, s>>>(ctl, dim, V);
-    lg_rhs<<<ga, kApplyThreads, 0, s>>>(ctl, p->P, rec, V, kTimeNew, 0, 1, 0);
+    LAUNCHED();
+    lg_launch_rhs(p, ctl, rec, V, R, ga, kTimeNew, 0, 1, 0);
     lg_final5b<<<gs, kLgThreads, 0, s>>>(ctl, dim);
-    lg_ctl_decide<<<1, 1, 0, s>>>(ctl, dim);
-    for (int k = 0; k < 4; ++k) LAUNCHED();
+    LAUNCHED();
+    lg_sync_ranks(p, ctl, R);  // partial sums of every rank are complete
+    lg_ctl_decide<<<1, 1, 0, s>>>(ctl, dim_total);
+    LAUNCHED();
   } else {
     for (int st = 0; st < 11; ++st) {
       const int dst = (st == 9) ? 1 : (st == 10) ? 2 : st + 1;
       lg_combine<<<gs, kLgThreads, 0, s>>>(ctl, dim, V, kTimeStage, st);
-      lg_rhs<<<ga, kApplyThreads, 0, s>>>(ctl, p->P, rec, V, kTimeStage, st, dst, 0);
       LAUNCHED();
-      LAUNCHED();
+      lg_launch_rhs(p, ctl, rec, V, R, ga, kTimeStage, st, dst, 0);
     }
     lg_final853<<<gs, kLgThreads, 0, s>>>(ctl, dim, V);
-    lg_ctl_decide<<<1, 1, 0, s>>>(ctl, dim);
-    lg_rhs<<<ga, kApplyThreads, 0, s>>>(ctl, p->P, rec, V, kTimeNew, 0, 3, 1);
+    LAUNCHED();
+    lg_sync_ranks(p, ctl, R);
+    lg_ctl_decide<<<1, 1, 0, s>>>(ctl, dim_total);
+    LAUNCHED();
+    lg_launch_rhs(p, ctl, rec, V, R, ga, kTimeNew, 0, 3, 1);
     lg_stnum853<<<gs, kLgThreads, 0, s>>>(ctl, dim);
+    LAUNCHED();
+    lg_sync_ranks(p, ctl, R);
     lg_ctl_end853<<<1, 1, 0, s>>>(ctl);
-    for (int k = 0; k < 5; ++k) LAUNCHED();
+    LAUNCHED();
   }
 }
 
+// shard context of one evolve call (null = the state is not sharded); pointers are device pointers
+struct LgShard {
+  int world, rank, n_total;
+  cplx* ys;                       // this rank's stage-input buffer (peer-visible)
+  const cplx* partners[3];        // ys of rank ^ (1 << b)
+  double* partial;                // this rank's partial-sum array (peer-visible)
+  double* peer_partial[8];
+  unsigned long long* peer_flag[8];
+};
+
 static int evolve_large_device(bqa_plan* p, const double* d_records, const std::vector<int64_t>& h_off,
                                const double* h_records, int n_tasks, const bqa_solver_opts* o, const cplx* d_psi0,
-                               int psi0_mode, const double* h_times, int n_times, cplx* d_out, TaskStats* d_stats) {
+                               int psi0_mode, const double* h_times, int n_times, cplx* d_out, TaskStats* d_stats,
+                               const LgShard* sh = nullptr) {
   const int64_t dim = p->P.dim;
+  const int world = sh ? sh->world : 1;
+  const int64_t dim_total = dim * world;
   const bool d5 = o->solver == BQA_SOLVER_DOPRI5;
   const int n_vec = d5 ? 9 : 12;
   cudaStream_t s = p->stream;
@@ -50,9 +101,29 @@ static int evolve_large_device(bqa_plan* p, const double* d_records, const std::
   LargeCtrl* ctl = nullptr;
   double* partial = nullptr;
   int* h_done = nullptr;
+  // RHS form: shared-memory-tiled passes when the operator allows it (always for a sharded state)
+  LgRhsPlan R;
+  R.world = world;
+  R.tile_grid = (int)std::min<int64_t>(std::max<int64_t>(dim >> kTileBits, 1), p->sm_count);
+  if (!o->interaction_picture && p->P.full_space && p->P.n_level == 2 && p->P.n_csr == 0 &&
+      (sh || !getenv("BQA_NO_TILED")))
+    R.tiled = tiled_plan(p->P.n_atoms, sh ? sh->n_total : p->P.n_atoms, sh ? sh->rank : 0, sh ? sh->partners : nullptr,
+                         0, R.passes);
+  if (sh && !R.tiled)
+    return fail("sharded evolve needs a two-level full space with >= 14 local atoms, no CSR term, Schroedinger picture");
+  if (R.tiled) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      CK(cudaFuncSetAttribute(lg_rhs_tiled, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileDynSmem));
+      attr_set = true;
+    }
+  }
   CK(cudaMalloc(&work, sizeof(cplx) * dim * n_vec));
   CK(cudaMalloc(&ctl, sizeof(LargeCtrl)));
-  CK(cudaMalloc(&partial, sizeof(double) * 4 * gs));
+  if (sh)
+    partial = sh->partial;
+  else
+    CK(cudaMalloc(&partial, sizeof(double) * 4 * gs));
   CK(cudaMallocHost(&h_done, 2 * sizeof(int)));
   int rc = 0;
   const int steps_per_poll = dim >= (1 << 22) ? 4 : (dim >= (1 << 16) ? 16 : 64);
@@ -65,13 +136,22 @@ static int evolve_large_device(bqa_plan* p, const double* d_records, const std::
     hc.o = default_opts(o->solver, o->atol, o->rtol, o->nsteps, o->interaction_picture);
     hc.o.reject_mode = o->reject_mode;
     for (int v = 0; v < n_vec; ++v) hc.vec[v] = work + (int64_t)v * dim;
+    if (sh) {
+      hc.vec[kVecYs] = sh->ys;
+      hc.world = sh->world;
+      hc.rank = sh->rank;
+      for (int r = 0; r < sh->world; ++r) {
+        hc.peer_partial[r] = sh->peer_partial[r];
+        hc.peer_flag[r] = sh->peer_flag[r];
+      }
+    }
     hc.partial = partial;
     hc.n_blocks = gs;
     hc.active = 1;
     if (cudaMemcpyAsync(ctl, &hc, sizeof(hc), cudaMemcpyHostToDevice, s) != cudaSuccess) { rc = fail("ctl upload failed"); break; }
     if (cudaStreamSynchronize(s) != cudaSuccess) { rc = fail("sync failed"); break; }  // hc is a stack object
     if (psi0_mode == 0) {
-      lg_init_state<<<gs, kLgThreads, 0, s>>>(hc.vec[kVecY], dim);
+      lg_init_state<<<gs, kLgThreads, 0, s>>>(hc.vec[kVecY], dim, sh ? sh->rank : 0);
       LAUNCHED();
     } else {
       const cplx* src = d_psi0 + (psi0_mode == 2 ? (int64_t)task * dim : 0);
@@ -86,16 +166,18 @@ static int evolve_large_device(bqa_plan* p, const double* d_records, const std::
         ran = 1;
         lg_ctl_begin<<<1, 1, 0, s>>>(ctl, t_cur, t_next);
         lg_combine<<<gs, kLgThreads, 0, s>>>(ctl, dim, V, kTimeX, -1);
-        lg_rhs<<<ga, kApplyThreads, 0, s>>>(ctl, p->P, rec, V, kTimeX, 0, 0, 0);
+        lg_launch_rhs(p, ctl, rec, V, R, ga, kTimeX, 0, 0, 0);
         lg_hinit_reduce<<<gs, kLgThreads, 0, s>>>(ctl, dim, 0);
+        lg_sync_ranks(p, ctl, R);
         lg_ctl_hinit<<<1, 1, 0, s>>>(ctl, 0);
         lg_combine<<<gs, kLgThreads, 0, s>>>(ctl, dim, V, kTimeHinit, -2);
-        lg_rhs<<<ga, kApplyThreads, 0, s>>>(ctl, p->P, rec, V, kTimeHinit, 0, 1, 0);
+        lg_launch_rhs(p, ctl, rec, V, R, ga, kTimeHinit, 0, 1, 0);
         lg_hinit_reduce<<<gs, kLgThreads, 0, s>>>(ctl, dim, 1);
+        lg_sync_ranks(p, ctl, R);
         lg_ctl_hinit<<<1, 1, 0, s>>>(ctl, 1);
-        for (int q = 0; q < 9; ++q) LAUNCHED();
+        for (int q = 0; q < 7; ++q) LAUNCHED();
         for (;;) {
-          for (int q = 0; q < steps_per_poll; ++q) lg_enqueue_step(p, ctl, rec, V, d5, gs, ga);
+          for (int q = 0; q < steps_per_poll; ++q) lg_enqueue_step(p, ctl, rec, V, d5, gs, ga, R, dim_total);
           cudaMemcpyAsync(h_done, (const char*)ctl + offsetof(LargeCtrl, c) + offsetof(Controller, status),
                           2 * sizeof(int), cudaMemcpyDeviceToHost, s);
           cudaError_t e = cudaStreamSynchronize(s);
@@ -115,7 +197,7 @@ static int evolve_large_device(bqa_plan* p, const double* d_records, const std::
   }
   cudaFree(work);
   cudaFree(ctl);
-  cudaFree(partial);
+  if (!sh) cudaFree(partial);
   cudaFreeHost(h_done);
   return rc;
 }

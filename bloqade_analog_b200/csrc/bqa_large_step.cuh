@@ -145,7 +145,10 @@ __global__ void lg_ctl_decide(LargeCtrl* ctl, int64_t dim) {
   lg_total3(ctl, a, b, s3);
   if (o.solver == kSolverDopri5) {
     double stden = 0.0;
-    for (int k = 0; k < ctl->n_blocks; ++k) stden += ctl->partial[3 * ctl->n_blocks + k];
+    for (int r = 0; r < (ctl->world > 1 ? ctl->world : 1); ++r) {
+      const volatile double* part = lg_partial_of(ctl, r);
+      for (int k = 0; k < ctl->n_blocks; ++k) stden += part[3 * ctl->n_blocks + k];
+    }
     c.nfcn += 6;
     const int acc = c.decide(o, c.err_dopri5(a, 2 * dim));
     ctl->accepted = acc;
@@ -215,9 +218,10 @@ lg_emit(LargeCtrl* ctl, int64_t dim, const double* __restrict__ V, double t, cpl
   }
 }
 
-__global__ void lg_init_state(cplx* y, int64_t dim) {
+// |0...0> (of a sharded state: the unit amplitude is on rank 0)
+__global__ void lg_init_state(cplx* y, int64_t dim, int rank) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < dim; i += (int64_t)gridDim.x * blockDim.x)
-    y[i] = cmake(i == 0 ? 1.0 : 0.0, 0.0);
+    y[i] = cmake((i == 0 && rank == 0) ? 1.0 : 0.0, 0.0);
 }
 
 }  // namespace bqa

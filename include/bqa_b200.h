@@ -167,6 +167,45 @@ int bqa_local_trace(bqa_plan* plan, const void* psi, int32_t mem, int32_t n_site
 int bqa_sample(bqa_plan* plan, const void* psi, int32_t n_states, const double* uniforms, int32_t n_shots,
                int32_t project_hyperfine, uint8_t* shots, int32_t mem);
 
+/* ---- sharded full-space state (BASELINE config 5) ------------------------------
+ * No reference counterpart: the reference keeps the state in ONE NumPy array (emulate/ir/state_vector.py:88-90)
+ * and cannot hold 2^30 amplitudes with its CSR operators (emulate/codegen/hamiltonian.py:161).  Rank r of
+ * `world` = 2^g ranks (one process per GPU) owns the amplitudes whose top g index bits equal r (atom k <-> index
+ * bit k, atom_type.py:139,151); the plan of every rank describes the n_atoms_total - g LOCAL atoms, the task
+ * record all n_atoms_total atoms.  Flips of a rank-bit atom read the partner shard in place over NVLink peer
+ * access; reductions and barriers of the integrator are device initiated (no host round trip, no collective
+ * library on the data path).  Buffers other ranks must see are allocated with bqa_shard_alloc (cudaMalloc +
+ * CUDA IPC handle, zero filled); the 64-byte handles are exchanged by the host (torch.distributed
+ * all_gather_object) and opened with bqa_shard_open. */
+typedef struct {
+  int32_t world, rank;      /* world = 2, 4 or 8                                                          */
+  int32_t n_atoms_total;    /* atoms of the whole register                                                */
+  int32_t pad;
+  void* ys[8];              /* [rank]: that rank's stage-input buffer, local_dim complex128 (own or peer-mapped) */
+  void* sync[8];            /* [rank]: that rank's sync block, bqa_shard_sync_bytes() bytes                */
+} bqa_shard_desc;
+
+int64_t bqa_shard_sync_bytes(void);
+int bqa_shard_alloc(int64_t bytes, void** dev_ptr, void* handle64);
+int bqa_shard_open(const void* handle64, void** peer_ptr);
+int bqa_shard_close(void* peer_ptr);
+int bqa_shard_free(void* dev_ptr);
+/* van-der-Waals diagonal of this rank's shard, same pair order as hamiltonian.py:76-89; pair_host is
+ * [n_atoms_total][n_atoms_total] */
+int bqa_plan_build_rydberg_shard(bqa_plan* plan, int32_t n_atoms_total, const double* pair_host, int32_t rank,
+                                 int32_t* diag_id);
+/* out_local = [-i] (H(t) psi)_local; partners[b] = device pointer of the shard of rank ^ (1 << b); the caller
+ * guarantees those shards are complete (no barrier inside).  Device pointers only. */
+int bqa_apply_sharded(bqa_plan* plan, const double* record, int64_t record_len, double t, int32_t raw,
+                      int32_t n_atoms_total, int32_t rank, const void* const* partners, const void* psi_in,
+                      void* psi_out);
+/* AnalogGate._apply (state_vector.py:574-602) for one sharded state; every rank calls it with the same record,
+ * options and times.  psi0_local: device pointer of this rank's shard, or NULL for |0...0>; psi_out_local:
+ * device, [n_times][local_dim]; stats: host, [n_times]. */
+int bqa_evolve_sharded(bqa_plan* plan, const double* record, int64_t record_len, const bqa_solver_opts* opts,
+                       const bqa_shard_desc* shard, const void* psi0_local, const double* times, int32_t n_times,
+                       void* psi_out_local, bqa_task_stats* stats);
+
 #ifdef __cplusplus
 }
 #endif
