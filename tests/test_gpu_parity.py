@@ -3,6 +3,7 @@ against (a) golden vectors produced by the reference itself (tests/golden/*.npz,
 (b) the CPU oracle (oracle/) on seeded inputs.  Bars: subspace / diagonal / shots bit-exact; single
 H psi <= 1e-13 relative; final states fidelity deviation < 1e-8 (north_star); observables 1e-7.
 """
+import os
 import numpy as np
 import pytest
 from conftest import GOLDEN_CASES, SMALL_CASES, cuda_available, golden_case, infidelity
@@ -506,3 +507,27 @@ def test_launch_counter_and_no_cpu_fallback():
     h = ham("c1_square3_a5")
     h._apply(golden_case("c1_square3_a5").data["rhs_psi"], 1.0)
     assert _lib.launch_count() > before
+
+
+def test_sharded_evolve_two_gpus_matches_unsharded():
+    """the real multi-GPU path (CUDA IPC peer mappings, device-initiated barriers, cross-rank error norms) under
+    torchrun on 2 GPUs of this box; skipped on a single-GPU box (profiles/r01_shard_check_*.json hold the runs
+    made with gpurun --gpus 2/4/8)"""
+    import json
+    import subprocess
+    import sys
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29541", os.path.join(root, "profiles", "shard_check.py"), "16", "0.2"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
+    assert lines, out.stderr[-2000:]
+    res = json.loads(lines[-1])
+    assert res["stats"]["status"] == 1
+    assert res["apply_max_rel_err"] < 1e-13
+    assert res["infidelity"] < 1e-8
+    assert res["shots_rows_differing"] <= 1
