@@ -57,7 +57,11 @@ static bool tiled_plan(int n_loc, int n_total, int64_t rank, const cplx* const* 
   int k = std::max(1, g);
   while (kTileBits + (kTileBits - 2) * (k - 1) + (k - g) < n_loc) ++k;
   const int local_extras = std::max(0, n_loc - (kTileBits + (kTileBits - 2) * (k - 1)));
-  const int n_tiled = n_loc - local_extras;
+  // unsharded: the leftover atom of the first pass is atom 13, i.e. the neighbouring tile (TileSpec::pair);
+  // the remaining leftovers are the top local atoms
+  const bool pair = g == 0 && local_extras > 0 && !getenv("BQA_TILED_NO_PAIR");
+  const int top_extras = local_extras - (pair ? 1 : 0);
+  const int n_tiled = n_loc - top_extras;
   int next = 0;
   for (int i = 0; i < k; ++i) {
     TileSpec s{};
@@ -65,7 +69,7 @@ static bool tiled_plan(int n_loc, int n_total, int64_t rank, const cplx* const* 
       s.lo_bits = kTileBits;
       s.hb = kTileBits;
       s.first = 1;
-      next = kTileBits;
+      next = kTileBits + (pair ? 1 : 0);
     } else {
       // `fresh` new atoms; the high group is widened downwards to at least 4 bits (lo_bits <= 9) over atoms
       // already done, which p0 then skips
@@ -81,9 +85,13 @@ static bool tiled_plan(int n_loc, int n_total, int64_t rank, const cplx* const* 
       s.n_x = 1;
       s.xbit = n_loc + i;
       s.x_ptr = partners[i];
-    } else if (i - g < local_extras) {
+    } else if (pair && i == 0) {
       s.n_x = 1;
-      s.xbit = n_loc - 1 - (i - g);
+      s.xbit = kTileBits;
+      s.pair = 1;
+    } else if (i - g - (pair ? 1 : 0) < top_extras) {
+      s.n_x = 1;
+      s.xbit = n_loc - 1 - (i - g - (pair ? 1 : 0));
     }
     s.n_total = n_total;
     s.idx_hi = (long long)(rank << n_loc);
@@ -101,23 +109,34 @@ static bool tiled_passes(const bqa_plan* p, int raw, std::vector<TileSpec>& pass
   return tiled_plan(P.n_atoms, P.n_atoms, 0, nullptr, raw, passes);
 }
 
-static int tiled_smem_attr() {
+typedef void (*TiledKernel)(const PlanView, const double*, const double*, double, const TileSpec, const cplx*, cplx*);
+
+// kernel variant of one pass: real / complex coefficients, first / later pass, with / without a leftover atom
+static TiledKernel tiled_kernel_for(bool real, const TileSpec& s) {
+#define BQA_TILED_VARIANTS(K, R)                                                                              \
+  K<R, false, false, false>, K<R, false, true, false>, K<R, false, false, true>, K<R, false, true, true>, \
+      K<R, true, false, false>, K<R, true, true, false>
+  static const TiledKernel tab[12] = {BQA_TILED_VARIANTS(apply_tiled_kernel, false),
+                                      BQA_TILED_VARIANTS(apply_tiled_kernel, true)};
   static bool attr_set = false;
   if (!attr_set) {
-    CK(cudaFuncSetAttribute(apply_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileDynSmem));
+    for (TiledKernel k : tab)
+      if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileDynSmem) != cudaSuccess) return nullptr;
     attr_set = true;
   }
-  return 0;
+  return tab[tiled_variant(real, s)];
 }
 
-// out = [-i] H(t) psi by tiled passes; `in` and `out` must not alias
-static int apply_tiled_launch(bqa_plan* p, const std::vector<TileSpec>& passes, const double* d_rec, const double* V,
-                              double t, const cplx* in, cplx* out) {
-  if (tiled_smem_attr()) return 1;
+// out = [-i] H(t) psi by tiled passes; `in` and `out` must not alias.  rec_host: the same record on the host
+static int apply_tiled_launch(bqa_plan* p, const std::vector<TileSpec>& passes, const double* rec_host,
+                              const double* d_rec, const double* V, double t, const cplx* in, cplx* out) {
+  const bool real = !record_has_phase(rec_host);
   const int64_t n_tiles = p->P.dim >> kTileBits;
   const int grid = (int)std::min<int64_t>(n_tiles, p->sm_count);
   for (const TileSpec& s : passes) {
-    apply_tiled_kernel<<<grid, kTileThreads, kTileDynSmem, p->stream>>>(p->P, d_rec, V, t, s, in, out);
+    TiledKernel kern = tiled_kernel_for(real, s);
+    if (!kern) return fail("apply_tiled: cannot raise the dynamic shared memory limit");
+    kern<<<grid, kTileThreads, kTileDynSmem, p->stream>>>(p->P, d_rec, V, t, s, in, out);
     LAUNCHED();
   }
   CK(cudaGetLastError());
@@ -194,7 +213,7 @@ int bqa_apply(bqa_plan* p, const double* record, int64_t record_len, double t, i
   const int mode = (raw ? 1 : 0) | (interaction ? 2 : 0);
   std::vector<TileSpec> passes;
   if (!interaction && src != (const cplx*)out.dev && tiled_passes(p, raw ? 1 : 0, passes)) {
-    if (apply_tiled_launch(p, passes, (const double*)rec.dev, V, t, src, (cplx*)out.dev)) return 1;
+    if (apply_tiled_launch(p, passes, record, (const double*)rec.dev, V, t, src, (cplx*)out.dev)) return 1;
   } else {
     apply_kernel<<<grid_for(p, dim, kApplyThreads), kApplyThreads, 0, p->stream>>>(
         p->P, (const double*)rec.dev, V, nullptr, t, mode, src, (cplx*)out.dev, nullptr);

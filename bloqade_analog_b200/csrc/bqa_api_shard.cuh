@@ -122,7 +122,7 @@ int bqa_apply_sharded(bqa_plan* p, const double* record, int64_t record_len, dou
   std::vector<TileSpec> passes;
   if (!tiled_plan(p->P.n_atoms, n_atoms_total, rank, pp, raw ? 1 : 0, passes))
     return fail("bqa_apply_sharded: needs at least 14 local atoms");
-  if (apply_tiled_launch(p, passes, (const double*)rec.dev, V, t, (const cplx*)psi_in, (cplx*)psi_out)) return 1;
+  if (apply_tiled_launch(p, passes, record, (const double*)rec.dev, V, t, (const cplx*)psi_in, (cplx*)psi_out)) return 1;
   CK(cudaStreamSynchronize(p->stream));
   return 0;
 }

@@ -29,8 +29,9 @@ constexpr int kTileBits = 13;
 constexpr int kTileThreads = 512;
 constexpr int kTileGroup = 2;
 constexpr int kTilePer = (1 << kTileBits) / kTileThreads;  // 16 amplitudes per thread
-constexpr int kTileSpare = 11;                             // of which this many are prefetched into shared memory
-constexpr size_t kTileDynSmem = sizeof(double) * 2 * kTileThreads * (kTilePer + kTileSpare);
+constexpr int kTileSpare = 12;                             // of which this many are prefetched into shared memory
+constexpr int kTileSlots = kTilePer + kTileSpare;          // ring of 8 KB slots (512 amplitudes each)
+constexpr size_t kTileSlotBytes = sizeof(double) * 2 * kTileThreads * kTileSlots;
 
 struct TileSpec {
   int lo_bits;   // tile bits [0, lo_bits); <= 9 unless first
@@ -38,6 +39,7 @@ struct TileSpec {
   int p0;        // tile bits [p0, 13) are flipped in this pass (0 in the first pass)
   int n_x;       // 0 or 1 leftover atom whose partner is gathered from global memory in this pass
   int xbit;
+  int pair;      // the leftover atom is index bit 13 of the first pass: tiles are walked in neighbouring pairs
   int first;     // first pass: out = (diag psi + flips); otherwise out += flips
   int last;      // last pass: multiply by -i unless raw
   int raw;
@@ -51,8 +53,9 @@ struct TileSpec {
 struct TileShared {
   Coefs cf;
   double crp[16], cip[16];     // coefficient of tile bit p (atom p, or hb + p - lo_bits)
-  double tabL[128], tabH[64];  // detuning sums of the tile-index bits (low 7 / high 6), first pass
+  double tabK[16];             // first pass: detuning sums of tile bits 9..12 (the amplitude number k of a thread)
 };
+constexpr size_t kTileDynSmem = kTileSlotBytes + sizeof(TileShared);  // the ring, then the tables
 
 __device__ __forceinline__ int64_t tile_base(const TileSpec& S, int64_t tile) {
   const int mid = S.hb - S.lo_bits;  // free bits between the two tile groups
@@ -63,27 +66,91 @@ __device__ __forceinline__ int64_t tile_base(const TileSpec& S, int64_t tile) {
 __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* g) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(g) : "memory");
 }
+// Explicit state-space loads for the tile loop.  `volatile` (no memory clobber) keeps them in program order
+// relative to each other and to the barriers: the side-stream requests of a quad are issued before its
+// shared-memory loads, and no generic-to-shared address conversion is generated.
+__device__ __forceinline__ cplx lds_cplx(uint32_t saddr) {
+  cplx z;
+  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(z.re), "=d"(z.im) : "r"(saddr));
+  return z;
+}
+__device__ __forceinline__ double lds_f64(uint32_t saddr) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(saddr));
+  return v;
+}
+__device__ __forceinline__ cplx ldg_cplx(const cplx* g) {
+  cplx z;
+  asm volatile("ld.global.v2.f64 {%0, %1}, [%2];" : "=d"(z.re), "=d"(z.im) : "l"(g));
+  return z;
+}
+__device__ __forceinline__ double ldg_f64(const double* g) {
+  double v;
+  asm volatile("ld.global.nc.f64 %0, [%1];" : "=d"(v) : "l"(g));
+  return v;
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-template <bool kReal, bool kFirst>
+// Tile walked by a CTA at iteration `it` (-1: none left).  Plain passes stride the tiles by the grid; a pass
+// whose leftover atom is the NEIGHBOURING tile (S.pair: index bit 13 in the first pass) walks tile pairs
+// (2q, 2q+1) back to back, so the partner tile of either is the one this CTA is fetching / has just fetched
+// and the leftover gather is served by L2 instead of DRAM.
+__device__ __forceinline__ int64_t tile_seq(const TileSpec& S, int64_t it, int64_t n_tiles) {
+  if (S.pair) {
+    const int64_t q = blockIdx.x + (it >> 1) * (int64_t)gridDim.x;
+    return q < (n_tiles >> 1) ? 2 * q + (it & 1) : -1;
+  }
+  const int64_t t = blockIdx.x + it * (int64_t)gridDim.x;
+  return t < n_tiles ? t : -1;
+}
+
+// A thread owns tile elements tid + 512 k, k = 0..15, and works on them in QUADS k = 4 g + j: the four
+// amplitudes of a quad differ in tile bits 9 and 10, so those two flips are register moves; the other flips
+// are one LDS.128 per amplitude and the coefficient of a flip is fetched once per quad.  The side streams of
+// a quad (V or the partial result, and the leftover-atom partner) are requested when the quad starts and
+// consumed when it ends.
+//
+// Shared memory is a ring of 28 slots of 512 amplitudes: the current tile sits in 16 of them, the next one
+// arrives by cp.async in the 12 free ones while quads 0..2 are computed and in the first 4 slots of the
+// current tile while its last quad is computed, so nothing is copied between tiles or parked in registers.
+//
+// One kernel per variant (real / complex coefficients, first / later pass, leftover atom or not; the host picks):
+// operands that are kernel parameters stay in the constant bank, and every variant gets its own register
+// allocation - folded into one kernel, the variants spilled inside the tile loop.
+template <bool kReal, bool kFirst, bool kHasX, bool kWide>
 __device__ __forceinline__ void apply_tiled_body(const int64_t dim, const int n, const double* __restrict__ V,
                                                  const TileSpec& S, const cplx* __restrict__ in,
-                                                 cplx* __restrict__ out, unsigned char* tile_bytes, TileShared& sh) {
+                                                 cplx* __restrict__ out) {
+  extern __shared__ __align__(16) unsigned char tile_bytes[];
+  const TileShared& sh = *reinterpret_cast<const TileShared*>(tile_bytes + kTileSlotBytes);
+  constexpr int kQuad = 4, kQuads = kTilePer / kQuad;
+  constexpr uint32_t kSlotBytes = kTileThreads * (uint32_t)sizeof(cplx);
   const uint32_t tid = threadIdx.x;
-  const int p0 = kFirst ? 0 : S.p0;
-  const bool has_x = S.n_x > 0;
+  const uint32_t tb16 = tid * (uint32_t)sizeof(cplx);
+  // kWide: a later pass with all 11 fresh atoms (p0 == 2), the shape of every later pass of a big state
+  const int p0 = kFirst ? 0 : (kWide ? 2 : S.p0);
   const int xb = S.xbit;
   const bool rot = S.last && !S.raw;
   const int64_t n_tiles = dim >> kTileBits;
-  int64_t tile = blockIdx.x;
-  if (tile >= n_tiles) return;
-  cplx* T = reinterpret_cast<cplx*>(tile_bytes);
-  cplx* Sp = T + (1 << kTileBits);  // spare: amplitudes k < kTileSpare of the next tile
+  int64_t it = 0;
+  int64_t tile = tile_seq(S, 0, n_tiles);
+  if (tile < 0) return;
   // amplitude k of this thread is tile element tid + 512 k, at global offset off0 + k * stride from the tile base
   const uint32_t off0 = kFirst ? tid : ((tid & ((1u << S.lo_bits) - 1u)) | ((tid >> S.lo_bits) << S.hb));
   const uint32_t stride = kFirst ? (uint32_t)kTileThreads : (((uint32_t)kTileThreads >> S.lo_bits) << S.hb);
-  const uint32_t sp_addr = (uint32_t)__cvta_generic_to_shared(Sp + tid);
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(tile_bytes);  // not 8 KB aligned: XOR offsets, then add
+  const uint32_t smem0 = sbase + tb16;
+  const uint32_t s_crp = sbase + (uint32_t)(kTileSlotBytes + offsetof(TileShared, crp));
+  const uint32_t s_cip = sbase + (uint32_t)(kTileSlotBytes + offsetof(TileShared, cip));
+  const uint32_t s_tabk = sbase + (uint32_t)(kTileSlotBytes + offsetof(TileShared, tabK));
+  uint32_t s0 = 0;  // ring slot of amplitude k = 0 of the current tile (uniform over the CTA)
+  // byte offset of the slot holding amplitude k of the current tile; k in [16, 32) addresses the next tile
+  auto slot = [&](int k) -> uint32_t {
+    uint32_t q = s0 + (uint32_t)k;
+    q -= q >= 2u * kTileSlots ? 2u * kTileSlots : (q >= (uint32_t)kTileSlots ? (uint32_t)kTileSlots : 0u);
+    return q * kSlotBytes;
+  };
   {
     const cplx* src = in + tile_base(S, tile) + off0;
 #pragma unroll
@@ -92,164 +159,194 @@ __device__ __forceinline__ void apply_tiled_body(const int64_t dim, const int n,
 #pragma unroll
       for (int k = 0; k < kTilePer / 2; ++k) tmp[k] = src[(size_t)(h * (kTilePer / 2) + k) * stride];
 #pragma unroll
-      for (int k = 0; k < kTilePer / 2; ++k) T[tid + (h * (kTilePer / 2) + k) * kTileThreads] = tmp[k];
+      for (int k = 0; k < kTilePer / 2; ++k)
+        *reinterpret_cast<cplx*>(tile_bytes + (h * (kTilePer / 2) + k) * kSlotBytes + tb16) = tmp[k];
     }
   }
+  double dl = 0.0;  // detuning of the tile bits held in the thread index (first pass: atoms 0..8)
+  if (kFirst) {
+#pragma unroll
+    for (int p = 0; p < 9; ++p)
+      if ((tid >> p) & 1) dl += sh.cf.delta[0][p];
+  }
   __syncthreads();
-  for (; tile < n_tiles; tile += gridDim.x) {
+  for (;;) {
     const int64_t base = tile_base(S, tile);
-    const int64_t next = tile + gridDim.x;
-    const bool has_next = next < n_tiles;
-    cplx pre[kTilePer - kTileSpare];
-    if (has_next) {
-      const cplx* src = in + tile_base(S, next) + off0;
-#pragma unroll
-      for (int k = 0; k < kTileSpare; ++k)
-        cp_async16(sp_addr + k * kTileThreads * (uint32_t)sizeof(cplx), src + (size_t)k * stride);
-      cp_async_commit();
-#pragma unroll
-      for (int k = kTileSpare; k < kTilePer; ++k) pre[k - kTileSpare] = src[(size_t)k * stride];
-    }
-    // per-tile constants: detuning of the atoms outside the tile, leftover-atom partner and sign
+    const int64_t next = tile_seq(S, it + 1, n_tiles);
+    const bool has_next = next >= 0;
+    const cplx* nsrc = in + (has_next ? tile_base(S, next) : base) + off0;
+    // per-tile constants: detuning of the atoms outside the tile, leftover-atom coefficient and sign
     const int64_t gbase = base | (int64_t)S.idx_hi;  // index in the whole register
-    double dbase = 0.0;
+    double dbase = dl;
     if (kFirst) {
       for (int a = kTileBits; a < n; ++a)
         if ((gbase >> a) & 1) dbase += sh.cf.delta[0][a];
     }
-    const cplx* xin = (S.x_ptr ? S.x_ptr + base : in + (has_x ? (base ^ ((int64_t)1 << xb)) : base)) + off0;
     double xr = 0.0, xi = 0.0;
-    if (has_x) {
+    const cplx* xsrc = in;
+    if (kHasX) {
       xr = sh.cf.c_re[0][xb];
       xi = ((gbase >> xb) & 1) ? sh.cf.c_im[0][xb] : -sh.cf.c_im[0][xb];
+      xsrc = (S.x_ptr ? S.x_ptr + base : in + (base ^ ((int64_t)1 << xb))) + off0;
     }
-    const double* Vt = V ? V + base + off0 : nullptr;
+    const double* Vt = V + base + off0;
     cplx* out_t = out + base + off0;
-    // third stream of the pass (V in the first pass, the partial result afterwards) and the leftover-atom
-    // partner are read one group of amplitudes ahead of the shared-memory work
-    cplx oc[kTileGroup], xc[kTileGroup], on[kTileGroup], xn[kTileGroup];
-    auto load_group = [&](int k0, cplx* o, cplx* x) {
 #pragma unroll
-      for (int j = 0; j < kTileGroup; ++j) {
-        const size_t off = (size_t)(k0 + j) * stride;
+    for (int g = 0; g < kQuads; ++g) {
+      // the last quad reads ring slots 4..15 of this tile only: once every thread is past quad 2, slots
+      // 0..3 are dead and take the last 4 slots of the next tile
+      if (g == kQuads - 1 && has_next) __syncthreads();
+      // side streams of this quad: requested now, consumed after the flips
+      double vq[kQuad];
+      cplx oq[kQuad], xq[kQuad];
+#pragma unroll
+      for (int j = 0; j < kQuad; ++j) {
+        const size_t off = (size_t)(g * kQuad + j) * stride;
         if (kFirst)
-          o[j] = cmake(Vt ? Vt[off] : 0.0, 0.0);
+          vq[j] = V ? ldg_f64(Vt + off) : 0.0;
         else
-          o[j] = out_t[off];
-        if (has_x) x[j] = xin[off];
+          oq[j] = ldg_cplx(out_t + off);
+        if (kHasX) xq[j] = ldg_cplx(xsrc + off);
       }
-    };
-    load_group(0, oc, xc);
-#pragma unroll 1
-    for (int k0 = 0; k0 < kTilePer; k0 += kTileGroup) {
-      if (k0 + kTileGroup < kTilePer) load_group(k0 + kTileGroup, on, xn);
+      // a quarter of the next tile per quad, behind the latency-critical side streams (the whole tile at once
+      // is a 96 KB burst per SM that the side streams then queue behind)
+      if (has_next) {
 #pragma unroll
-      for (int j = 0; j < kTileGroup; ++j) {
-        const uint32_t e = tid + (k0 + j) * kTileThreads;
-        const uint32_t eb = e * (uint32_t)sizeof(cplx);
-        double ar, ai;
-        if (kFirst) {
-          const cplx own = *reinterpret_cast<const cplx*>(tile_bytes + eb);
-          const double diag = oc[j].re - (dbase + sh.tabL[e & 127] + sh.tabH[e >> 7]);
-          ar = diag * own.re;
-          ai = diag * own.im;
-        } else {
-          ar = oc[j].re;
-          ai = oc[j].im;
-        }
+        for (int k = g * kQuad; k < (g + 1) * kQuad; ++k) cp_async16(smem0 + slot(kTilePer + k), nsrc + (size_t)k * stride);
+        cp_async_commit();
+      }
+      cplx own[kQuad];
+      uint32_t eb[kQuad];
+      double ar[kQuad], ai[kQuad];
+      const bool need_own = kFirst || p0 <= 10;
 #pragma unroll
-        for (int p = 0; p < kTileBits; ++p) {
-          if (!kFirst && p < p0) continue;
-          const cplx z = *reinterpret_cast<const cplx*>(tile_bytes + (eb ^ ((uint32_t)sizeof(cplx) << p)));
-          const double cr = sh.crp[p];
+      for (int j = 0; j < kQuad; ++j) {
+        eb[j] = slot(g * kQuad + j) + tb16;
+        if (need_own) own[j] = lds_cplx(sbase + eb[j]);
+        ar[j] = 0.0;
+        ai[j] = 0.0;
+      }
+      // tile bits 9, 10: partners inside the quad
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int p = 9 + q;
+        if (!kFirst && p < p0) continue;
+        const double cr = lds_f64(s_crp + 8 * p), cim = kReal ? 0.0 : lds_f64(s_cip + 8 * p);
+#pragma unroll
+        for (int j = 0; j < kQuad; ++j) {
+          const cplx z = own[j ^ (1 << q)];
           if (kReal) {
-            ar = fma(cr, z.re, ar);
-            ai = fma(cr, z.im, ai);
+            ar[j] = fma(cr, z.re, ar[j]);
+            ai[j] = fma(cr, z.im, ai[j]);
           } else {
-            const double ci = ((e >> p) & 1) ? sh.cip[p] : -sh.cip[p];
-            ar = fma(cr, z.re, fma(-ci, z.im, ar));
-            ai = fma(cr, z.im, fma(ci, z.re, ai));
+            const double ci = ((j >> q) & 1) ? cim : -cim;
+            ar[j] = fma(cr, z.re, fma(-ci, z.im, ar[j]));
+            ai[j] = fma(cr, z.im, fma(ci, z.re, ai[j]));
           }
         }
-        if (has_x) {
-          ar = fma(xr, xc[j].re, fma(-xi, xc[j].im, ar));
-          ai = fma(xr, xc[j].im, fma(xi, xc[j].re, ai));
+      }
+      // the other tile bits: conflict-free LDS.128 partners
+#pragma unroll
+      for (int p = 0; p < kTileBits; ++p) {
+        if (p == 9 || p == 10) continue;
+        if (!kFirst && p < p0) continue;
+        const double cr = lds_f64(s_crp + 8 * p);
+        double ci = 0.0;
+        if (!kReal) {
+          const bool up = p < 9 ? ((tid >> p) & 1) : ((g >> (p - 11)) & 1);
+          const double cim = lds_f64(s_cip + 8 * p);
+          ci = up ? cim : -cim;
         }
-        out_t[(size_t)(k0 + j) * stride] = rot ? cmake(ai, -ar) : cmake(ar, ai);
+#pragma unroll
+        for (int j = 0; j < kQuad; ++j) {
+          const uint32_t pb = p < 9 ? (eb[j] ^ ((uint32_t)sizeof(cplx) << p))
+                                    : (slot((g * kQuad + j) ^ (1 << (p - 9))) + tb16);
+          const cplx z = lds_cplx(sbase + pb);
+          if (kReal) {
+            ar[j] = fma(cr, z.re, ar[j]);
+            ai[j] = fma(cr, z.im, ai[j]);
+          } else {
+            ar[j] = fma(cr, z.re, fma(-ci, z.im, ar[j]));
+            ai[j] = fma(cr, z.im, fma(ci, z.re, ai[j]));
+          }
+        }
       }
 #pragma unroll
-      for (int j = 0; j < kTileGroup; ++j) {
-        oc[j] = on[j];
-        xc[j] = xn[j];
+      for (int j = 0; j < kQuad; ++j) {
+        if (kFirst) {
+          const double diag = vq[j] - (dbase + lds_f64(s_tabk + 8 * (g * kQuad + j)));
+          ar[j] = fma(diag, own[j].re, ar[j]);
+          ai[j] = fma(diag, own[j].im, ai[j]);
+        } else {
+          ar[j] += oq[j].re;
+          ai[j] += oq[j].im;
+        }
+        if (kHasX) {
+          ar[j] = fma(xr, xq[j].re, fma(-xi, xq[j].im, ar[j]));
+          ai[j] = fma(xr, xq[j].im, fma(xi, xq[j].re, ai[j]));
+        }
+        out_t[(size_t)(g * kQuad + j) * stride] = rot ? cmake(ai[j], -ar[j]) : cmake(ar[j], ai[j]);
       }
     }
-    __syncthreads();  // everyone is done reading this tile
-    if (has_next) {
-      cp_async_wait_all();  // each thread moves only the slots it fetched itself: no barrier needed in between
-#pragma unroll
-      for (int k = 0; k < kTileSpare; ++k) T[tid + k * kTileThreads] = Sp[tid + k * kTileThreads];
-#pragma unroll
-      for (int k = kTileSpare; k < kTilePer; ++k) T[tid + k * kTileThreads] = pre[k - kTileSpare];
-    }
-    __syncthreads();
+    if (!has_next) break;
+    cp_async_wait_all();
+    __syncthreads();  // everyone is done reading this tile and the next one has landed
+    s0 += kTilePer;
+    if (s0 >= (uint32_t)kTileSlots) s0 -= kTileSlots;
+    tile = next;
+    ++it;
   }
 }
 
-// One CTA's share of a tiled pass: coefficients at time t, then the tile loop
+// One CTA's share of a tiled pass: coefficients at time t, then the tile loop.  kReal is the host's promise that
+// no Rabi term of the record carries a phase waveform (record_has_phase), i.e. every c_im is exactly zero.
+template <bool kReal, bool kFirst, bool kHasX, bool kWide>
 __device__ __forceinline__ void apply_tiled_cta(const PlanView& P, const double* __restrict__ rec,
                                                 const double* __restrict__ V, double t, const TileSpec& S,
                                                 const cplx* __restrict__ in, cplx* __restrict__ out) {
-  extern __shared__ __align__(16) unsigned char tile_smem[];
-  __shared__ TileShared sh;
-  __shared__ int s_complex;
+  extern __shared__ __align__(16) unsigned char tile_bytes[];
+  TileShared& sh = *reinterpret_cast<TileShared*>(tile_bytes + kTileSlotBytes);
   const int tid = threadIdx.x;
   const TaskView tv = task_view(rec);
   const int n = tv.n_atoms;  // whole register (> P.n_atoms for a sharded state)
-  if (tid == 0) s_complex = 0;
-  __syncthreads();
-  for (int e = tid; e < n; e += blockDim.x) {
-    coef_entry(tv, t, e, sh.cf);
-    if (sh.cf.c_im[0][e] != 0.0) s_complex = 1;
-  }
+  for (int e = tid; e < n; e += blockDim.x) coef_entry(tv, t, e, sh.cf);
   __syncthreads();
   auto atom_of = [&](int p) { return p < S.lo_bits ? p : S.hb + (p - S.lo_bits); };
   if (tid < kTileBits) {
     sh.crp[tid] = sh.cf.c_re[0][atom_of(tid)];
     sh.cip[tid] = sh.cf.c_im[0][atom_of(tid)];
   }
-  if (S.first) {
-    if (tid >= 32 && tid < 160) {
-      const int q = tid - 32;
-      double s = 0.0;
-      for (int p = 0; p < 7; ++p)
-        if ((q >> p) & 1) s += sh.cf.delta[0][atom_of(p)];
-      sh.tabL[q] = s;
-    } else if (tid >= 160 && tid < 224) {
-      const int q = tid - 160;
-      double s = 0.0;
-      for (int p = 0; p < 6; ++p)
-        if ((q >> p) & 1) s += sh.cf.delta[0][atom_of(7 + p)];
-      sh.tabH[q] = s;
-    }
+  if (kFirst && tid >= 32 && tid < 48) {
+    const int q = tid - 32;
+    double d = 0.0;
+    for (int p = 0; p < 4; ++p)
+      if ((q >> p) & 1) d += sh.cf.delta[0][atom_of(9 + p)];
+    sh.tabK[q] = d;
   }
   __syncthreads();
-  if (S.first) {
-    if (s_complex)
-      apply_tiled_body<false, true>(P.dim, n, V, S, in, out, tile_smem, sh);
-    else
-      apply_tiled_body<true, true>(P.dim, n, V, S, in, out, tile_smem, sh);
-  } else {
-    if (s_complex)
-      apply_tiled_body<false, false>(P.dim, n, V, S, in, out, tile_smem, sh);
-    else
-      apply_tiled_body<true, false>(P.dim, n, V, S, in, out, tile_smem, sh);
-  }
+  apply_tiled_body<kReal, kFirst, kHasX, kWide>(P.dim, n, V, S, in, out);
 }
 
+template <bool kReal, bool kFirst, bool kHasX, bool kWide>
 __global__ void __launch_bounds__(kTileThreads, 1)
 apply_tiled_kernel(const PlanView P, const double* __restrict__ rec, const double* __restrict__ V, double t,
                    const TileSpec S, const cplx* __restrict__ in, cplx* __restrict__ out) {
-  apply_tiled_cta(P, rec, V, t, S, in, out);
+  apply_tiled_cta<kReal, kFirst, kHasX, kWide>(P, rec, V, t, S, in, out);
+}
+
+// kernel variant index of a pass: bit 3 real coefficients, 2..0 = {later narrow, later narrow + x, later wide,
+// later wide + x, first, first + x}
+inline int tiled_variant(bool real, const TileSpec& s) {
+  const int shape = s.first ? 4 + (s.n_x > 0) : (s.p0 == 2 ? 2 : 0) + (s.n_x > 0);
+  return (real ? 6 : 0) + shape;
+}
+
+// host: does any Rabi term of this task record carry a phase waveform?  (No: all coefficients are real.)
+inline bool record_has_phase(const double* rec_host) {
+  const TaskView tv = task_view(rec_host);
+  for (int k = 0; k < tv.n_rabi; ++k)
+    if ((int)tv.rabi[(int64_t)k * (3 + tv.n_atoms) + 1] >= 0) return true;
+  return false;
 }
 
 }  // namespace bqa

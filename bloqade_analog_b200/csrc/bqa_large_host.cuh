@@ -8,7 +8,15 @@ struct LgRhsPlan {
   std::vector<TileSpec> passes;
   int world = 1;
   int tile_grid = 1;
+  bool real = false;  // no phase waveform in the current task record: real-coefficient kernels
 };
+
+typedef void (*LgTiledKernel)(LargeCtrl*, const PlanView, const double*, const double*, int, int, int, int, const TileSpec);
+
+static LgTiledKernel lg_tiled_kernel_at(int variant) {
+  static const LgTiledKernel tab[12] = {BQA_TILED_VARIANTS(lg_rhs_tiled, false), BQA_TILED_VARIANTS(lg_rhs_tiled, true)};
+  return tab[variant];
+}
 
 static void lg_sync_ranks(bqa_plan* p, LargeCtrl* ctl, const LgRhsPlan& R) {
   if (R.world <= 1) return;
@@ -23,7 +31,7 @@ static void lg_launch_rhs(bqa_plan* p, LargeCtrl* ctl, const double* rec, const 
   lg_sync_ranks(p, ctl, R);
   if (R.tiled) {
     for (const TileSpec& S : R.passes) {
-      lg_rhs_tiled<<<R.tile_grid, kTileThreads, kTileDynSmem, s>>>(ctl, p->P, rec, V, tmode, st, dst, cond, S);
+      lg_tiled_kernel_at(tiled_variant(R.real, S))<<<R.tile_grid, kTileThreads, kTileDynSmem, s>>>(ctl, p->P, rec, V, tmode, st, dst, cond, S);
       LAUNCHED();
     }
   } else {
@@ -114,7 +122,8 @@ static int evolve_large_device(bqa_plan* p, const double* d_records, const std::
   if (R.tiled) {
     static bool attr_set = false;
     if (!attr_set) {
-      CK(cudaFuncSetAttribute(lg_rhs_tiled, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileDynSmem));
+      for (int v = 0; v < 12; ++v)
+        CK(cudaFuncSetAttribute(lg_tiled_kernel_at(v), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileDynSmem));
       attr_set = true;
     }
   }
@@ -130,6 +139,7 @@ static int evolve_large_device(bqa_plan* p, const double* d_records, const std::
   for (int task = 0; task < n_tasks && !rc; ++task) {
     const double* rec = d_records + h_off[task];
     const int diag_id = (int)h_records[h_off[task] + 1];
+    R.real = !record_has_phase(h_records + h_off[task]);
     const double* V = (diag_id >= 0 && diag_id < (int)p->diags.size()) ? p->diags[diag_id] : nullptr;
     LargeCtrl hc;
     memset(&hc, 0, sizeof(hc));
