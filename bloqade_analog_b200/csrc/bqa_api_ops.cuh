@@ -48,20 +48,31 @@ static int sample_device(bqa_plan* p, const cplx* d_psi, int n_seg, const double
 // Shared-memory-tiled H(t) psi for large two-level full spaces (bqa_apply_tiled.cuh): pass list.
 // n_loc atoms are local to this device; atoms n_loc .. n_total-1 are the rank bits of a sharded state whose
 // partner shards are `partners[b]` (rank ^ (1 << b)); n_total == n_loc when not sharded.
+static int tiled_pass_count(int n_loc, int g, int maxfresh) {
+  int k = std::max(1, g);
+  while (kTileBits + maxfresh * (k - 1) + (k - g) < n_loc) ++k;
+  return k;
+}
+
 static bool tiled_plan(int n_loc, int n_total, int64_t rank, const cplx* const* partners, int raw,
                        std::vector<TileSpec>& passes) {
   if (n_loc <= kTileBits) return false;
   const int g = n_total - n_loc;
-  // k passes cover 13 + 11 (k - 1) tile bits plus ONE leftover atom each (partner amplitudes gathered from
-  // global memory: the peer shards first, then the top local atoms)
-  int k = std::max(1, g);
-  while (kTileBits + (kTileBits - 2) * (k - 1) + (k - g) < n_loc) ++k;
-  const int local_extras = std::max(0, n_loc - (kTileBits + (kTileBits - 2) * (k - 1)));
-  // unsharded: the leftover atom of the first pass is atom 13, i.e. the neighbouring tile (TileSpec::pair);
-  // the remaining leftovers are the top local atoms
-  const bool pair = g == 0 && local_extras > 0 && !getenv("BQA_TILED_NO_PAIR");
-  const int top_extras = local_extras - (pair ? 1 : 0);
+  // k passes cover 13 + maxfresh (k - 1) tile bits plus ONE leftover atom each (partner amplitudes gathered
+  // from global memory: the peer shards first, then local atoms).  A later pass takes 11 fresh atoms with
+  // 64-byte global segments (lo_bits = 2) or 10 with full 128-byte lines (lo_bits = 3): the latter when it
+  // does not cost a pass.
+  int maxfresh = kTileBits - 2;
+  if (!getenv("BQA_TILED_LO2") && tiled_pass_count(n_loc, g, maxfresh - 1) == tiled_pass_count(n_loc, g, maxfresh))
+    --maxfresh;
+  const int k = tiled_pass_count(n_loc, g, maxfresh);
+  const int local_extras = std::max(0, n_loc - (kTileBits + maxfresh * (k - 1)));
+  // unsharded: the leftover atom of the first pass is atom 13, i.e. the neighbouring tile; the remaining
+  // leftovers are the top local atoms.  Every local leftover is walked in partner pairs (TileSpec::pair).
+  const bool adj = g == 0 && local_extras > 0;
+  const int top_extras = local_extras - (adj ? 1 : 0);
   const int n_tiled = n_loc - top_extras;
+  const bool pairs = !getenv("BQA_TILED_NO_PAIR");
   int next = 0;
   for (int i = 0; i < k; ++i) {
     TileSpec s{};
@@ -69,11 +80,11 @@ static bool tiled_plan(int n_loc, int n_total, int64_t rank, const cplx* const* 
       s.lo_bits = kTileBits;
       s.hb = kTileBits;
       s.first = 1;
-      next = kTileBits + (pair ? 1 : 0);
+      next = kTileBits + (adj ? 1 : 0);
     } else {
       // `fresh` new atoms; the high group is widened downwards to at least 4 bits (lo_bits <= 9) over atoms
       // already done, which p0 then skips
-      const int fresh = std::min(n_tiled - next, kTileBits - 2);
+      const int fresh = std::min(n_tiled - next, maxfresh);
       const int tb = std::max(fresh, 4);
       s.lo_bits = kTileBits - tb;
       s.hb = next + fresh - tb;
@@ -85,13 +96,17 @@ static bool tiled_plan(int n_loc, int n_total, int64_t rank, const cplx* const* 
       s.n_x = 1;
       s.xbit = n_loc + i;
       s.x_ptr = partners[i];
-    } else if (pair && i == 0) {
+    } else if (adj && i == 0) {
       s.n_x = 1;
       s.xbit = kTileBits;
-      s.pair = 1;
-    } else if (i - g - (pair ? 1 : 0) < top_extras) {
+    } else if (i - g - (adj ? 1 : 0) < top_extras) {
       s.n_x = 1;
-      s.xbit = n_loc - 1 - (i - g - (pair ? 1 : 0));
+      s.xbit = n_loc - 1 - (i - g - (adj ? 1 : 0));
+    }
+    if (s.n_x && !s.x_ptr && pairs) {
+      // tile-index bit of the leftover atom: the free index bits are [lo_bits, hb) and [hb + tb, n_loc)
+      s.pair = 1;
+      s.pair_b = s.xbit < s.hb ? s.xbit - s.lo_bits : (s.hb - s.lo_bits) + (s.xbit - (s.hb + s.tb));
     }
     s.n_total = n_total;
     s.idx_hi = (long long)(rank << n_loc);
@@ -113,10 +128,10 @@ typedef void (*TiledKernel)(const PlanView, const double*, const double*, double
 
 // kernel variant of one pass: real / complex coefficients, first / later pass, with / without a leftover atom
 static TiledKernel tiled_kernel_for(bool real, const TileSpec& s) {
-#define BQA_TILED_VARIANTS(K, R)                                                                              \
-  K<R, false, false, false>, K<R, false, true, false>, K<R, false, false, true>, K<R, false, true, true>, \
-      K<R, true, false, false>, K<R, true, true, false>
-  static const TiledKernel tab[12] = {BQA_TILED_VARIANTS(apply_tiled_kernel, false),
+#define BQA_TILED_VARIANTS(K, R)                                                                          \
+  K<R, false, false, 0>, K<R, false, true, 0>, K<R, false, false, 2>, K<R, false, true, 2>, K<R, false, false, 3>, \
+      K<R, false, true, 3>, K<R, true, false, 0>, K<R, true, true, 0>
+  static const TiledKernel tab[16] = {BQA_TILED_VARIANTS(apply_tiled_kernel, false),
                                       BQA_TILED_VARIANTS(apply_tiled_kernel, true)};
   static bool attr_set = false;
   if (!attr_set) {

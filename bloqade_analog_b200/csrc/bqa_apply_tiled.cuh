@@ -39,7 +39,8 @@ struct TileSpec {
   int p0;        // tile bits [p0, 13) are flipped in this pass (0 in the first pass)
   int n_x;       // 0 or 1 leftover atom whose partner is gathered from global memory in this pass
   int xbit;
-  int pair;      // the leftover atom is index bit 13 of the first pass: tiles are walked in neighbouring pairs
+  int pair;      // the leftover atom is local: tiles are walked in partner pairs (t, t ^ (1 << pair_b))
+  int pair_b;    // bit of the TILE index that the leftover atom's index bit maps to
   int first;     // first pass: out = (diag psi + flips); otherwise out += flips
   int last;      // last pass: multiply by -i unless raw
   int raw;
@@ -93,13 +94,15 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 // Tile walked by a CTA at iteration `it` (-1: none left).  Plain passes stride the tiles by the grid; a pass
-// whose leftover atom is the NEIGHBOURING tile (S.pair: index bit 13 in the first pass) walks tile pairs
-// (2q, 2q+1) back to back, so the partner tile of either is the one this CTA is fetching / has just fetched
-// and the leftover gather is served by L2 instead of DRAM.
+// with a LOCAL leftover atom (S.pair) walks the two tiles that are each other's partner under that atom back
+// to back, so the leftover gather of either finds the tile this CTA is fetching / has just fetched in L2.
 __device__ __forceinline__ int64_t tile_seq(const TileSpec& S, int64_t it, int64_t n_tiles) {
   if (S.pair) {
     const int64_t q = blockIdx.x + (it >> 1) * (int64_t)gridDim.x;
-    return q < (n_tiles >> 1) ? 2 * q + (it & 1) : -1;
+    if (q >= (n_tiles >> 1)) return -1;
+    const int b = S.pair_b;
+    const int64_t t = ((q >> b) << (b + 1)) | (q & (((int64_t)1 << b) - 1));
+    return t | ((it & 1) << b);
   }
   const int64_t t = blockIdx.x + it * (int64_t)gridDim.x;
   return t < n_tiles ? t : -1;
@@ -118,7 +121,7 @@ __device__ __forceinline__ int64_t tile_seq(const TileSpec& S, int64_t it, int64
 // One kernel per variant (real / complex coefficients, first / later pass, leftover atom or not; the host picks):
 // operands that are kernel parameters stay in the constant bank, and every variant gets its own register
 // allocation - folded into one kernel, the variants spilled inside the tile loop.
-template <bool kReal, bool kFirst, bool kHasX, bool kWide>
+template <bool kReal, bool kFirst, bool kHasX, int kP0>
 __device__ __forceinline__ void apply_tiled_body(const int64_t dim, const int n, const double* __restrict__ V,
                                                  const TileSpec& S, const cplx* __restrict__ in,
                                                  cplx* __restrict__ out) {
@@ -128,8 +131,9 @@ __device__ __forceinline__ void apply_tiled_body(const int64_t dim, const int n,
   constexpr uint32_t kSlotBytes = kTileThreads * (uint32_t)sizeof(cplx);
   const uint32_t tid = threadIdx.x;
   const uint32_t tb16 = tid * (uint32_t)sizeof(cplx);
-  // kWide: a later pass with all 11 fresh atoms (p0 == 2), the shape of every later pass of a big state
-  const int p0 = kFirst ? 0 : (kWide ? 2 : S.p0);
+  // kP0 = 2 / 3: a later pass with 11 / 10 fresh atoms (the shapes of the later passes of a big state) gets
+  // compile-time loop bounds; kP0 = 0: read it from the pass description
+  const int p0 = kFirst ? 0 : (kP0 > 0 ? kP0 : S.p0);
   const int xb = S.xbit;
   const bool rot = S.last && !S.raw;
   const int64_t n_tiles = dim >> kTileBits;
@@ -300,7 +304,7 @@ __device__ __forceinline__ void apply_tiled_body(const int64_t dim, const int n,
 
 // One CTA's share of a tiled pass: coefficients at time t, then the tile loop.  kReal is the host's promise that
 // no Rabi term of the record carries a phase waveform (record_has_phase), i.e. every c_im is exactly zero.
-template <bool kReal, bool kFirst, bool kHasX, bool kWide>
+template <bool kReal, bool kFirst, bool kHasX, int kP0>
 __device__ __forceinline__ void apply_tiled_cta(const PlanView& P, const double* __restrict__ rec,
                                                 const double* __restrict__ V, double t, const TileSpec& S,
                                                 const cplx* __restrict__ in, cplx* __restrict__ out) {
@@ -324,21 +328,21 @@ __device__ __forceinline__ void apply_tiled_cta(const PlanView& P, const double*
     sh.tabK[q] = d;
   }
   __syncthreads();
-  apply_tiled_body<kReal, kFirst, kHasX, kWide>(P.dim, n, V, S, in, out);
+  apply_tiled_body<kReal, kFirst, kHasX, kP0>(P.dim, n, V, S, in, out);
 }
 
-template <bool kReal, bool kFirst, bool kHasX, bool kWide>
+template <bool kReal, bool kFirst, bool kHasX, int kP0>
 __global__ void __launch_bounds__(kTileThreads, 1)
 apply_tiled_kernel(const PlanView P, const double* __restrict__ rec, const double* __restrict__ V, double t,
                    const TileSpec S, const cplx* __restrict__ in, cplx* __restrict__ out) {
-  apply_tiled_cta<kReal, kFirst, kHasX, kWide>(P, rec, V, t, S, in, out);
+  apply_tiled_cta<kReal, kFirst, kHasX, kP0>(P, rec, V, t, S, in, out);
 }
 
-// kernel variant index of a pass: bit 3 real coefficients, 2..0 = {later narrow, later narrow + x, later wide,
-// later wide + x, first, first + x}
+// kernel variant index of a pass: 8 shapes {later p0 runtime, later p0 = 2, later p0 = 3, first} x {no x, x},
+// then real coefficients
 inline int tiled_variant(bool real, const TileSpec& s) {
-  const int shape = s.first ? 4 + (s.n_x > 0) : (s.p0 == 2 ? 2 : 0) + (s.n_x > 0);
-  return (real ? 6 : 0) + shape;
+  const int shape = s.first ? 6 : (s.p0 == 2 ? 2 : (s.p0 == 3 ? 4 : 0));
+  return (real ? 8 : 0) + shape + (s.n_x > 0 ? 1 : 0);
 }
 
 // host: does any Rabi term of this task record carry a phase waveform?  (No: all coefficients are real.)

@@ -14,7 +14,7 @@ struct LgRhsPlan {
 typedef void (*LgTiledKernel)(LargeCtrl*, const PlanView, const double*, const double*, int, int, int, int, const TileSpec);
 
 static LgTiledKernel lg_tiled_kernel_at(int variant) {
-  static const LgTiledKernel tab[12] = {BQA_TILED_VARIANTS(lg_rhs_tiled, false), BQA_TILED_VARIANTS(lg_rhs_tiled, true)};
+  static const LgTiledKernel tab[16] = {BQA_TILED_VARIANTS(lg_rhs_tiled, false), BQA_TILED_VARIANTS(lg_rhs_tiled, true)};
   return tab[variant];
 }
 
@@ -122,7 +122,7 @@ static int evolve_large_device(bqa_plan* p, const double* d_records, const std::
   if (R.tiled) {
     static bool attr_set = false;
     if (!attr_set) {
-      for (int v = 0; v < 12; ++v)
+      for (int v = 0; v < 16; ++v)
         CK(cudaFuncSetAttribute(lg_tiled_kernel_at(v), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileDynSmem));
       attr_set = true;
     }
