@@ -4,17 +4,18 @@
 // The one-pass kernel (apply_kernel) gathers 25 partners per element straight from global memory at 2^25:
 // ncu shows 4.2x the algorithmic DRAM traffic (profiles/r01_summary.md).  Here a CTA stages a TILE of 2^13
 // amplitudes (128 KB) in shared memory whose index bits are a contiguous low group [0, lo_bits) plus a high
-// group [hb, hb + tb): every flip of a tile bit is a conflict-free LDS.128.  Pass A (lo_bits = 13) adds the
-// diagonal and the flips of atoms 0..12 and writes H psi partially; pass B (lo_bits = 2 for 64-byte DRAM
-// segments, high group = atoms 13..23) accumulates the remaining flips into it and applies the -i factor;
-// one leftover atom per pass is gathered from global memory (atom 24 at n = 25).  DRAM traffic by design:
-// 40 + 48 + 16 = 104 B per amplitude.
+// group [hb, hb + tb): every flip of a tile bit is a conflict-free shared-memory load (or a register move).
+// Pass A (lo_bits = 13) adds the diagonal and the flips of atoms 0..12 and writes H psi partially; a later
+// pass (lo_bits = 3: full 128-byte DRAM lines, or 2 when the 11th fresh atom saves a pass) accumulates the
+// flips of its high group into it, the last one applies the -i factor.  Each pass may also take ONE leftover
+// atom whose partner amplitudes are gathered from global memory: atom 13 in pass A (the neighbouring tile),
+// a top atom (or, for a sharded state, a rank bit = the peer GPU's shard) in later passes.  DRAM traffic by
+// design at n = 25: 40 + 48 B per amplitude + what the two leftover gathers miss in L2 (measured 98 B).
 //
 // One CTA per SM (the tile takes most of the shared memory), so the CTA overlaps its own DRAM reads with its
-// shared-memory work: while tile i is computed, tile i+1 arrives by cp.async into the spare 88 KB of shared
-// memory (11 of the 16 amplitudes each thread owns) and in 20 registers (the other 5); the third stream of
-// the pass (V, or the partial result) is read one group of amplitudes ahead.  (L2 prefetch instructions were
-// tried instead - bulk and per line - and doubled the DRAM reads without producing hits: profiles/r01_summary.md.)
+// shared-memory work: see apply_tiled_body for the ring of slots and the per-quad request order.  (L2
+// prefetch instructions were tried - bulk and per line - and doubled the DRAM reads without producing hits;
+// side streams requested a further quad ahead cost more in registers than they hide: profiles/r01_summary.md.)
 //
 // Reference code replaced: RydbergHamiltonian._ode_complex_kernel / _apply (emulate/ir/state_vector.py:323-334,
 // 375-398) with IndexMapping / CSR matvecs of bit-flip form (emulate/sparse_operator.py:24-34,99-128).
