@@ -232,9 +232,9 @@ def hpsi_roofline(torch, device_index, peaks, peak_kind, n_atoms=25, reps=20):
     alg = 32.0 * dim
     ach = alg / (np.median(ms) * 1e-3) / 1e9
     tiled = n_atoms > 13 and not os.environ.get("BQA_NO_TILED")
-    # ncu --set full, 2^25: dram read+write of the two tiled passes (profiles/r01_summary.md: 1.55 GB + 1.75 GB);
+    # ncu --set full, 2^25: dram read+write of the two tiled passes (profiles/r01_summary.md: 1.39 GB + 1.67 GB);
     # one-pass gather kernel 4.54 GB
-    traffic = (3.30e9 if tiled else 4.54e9) if n_atoms == 25 else None
+    traffic = (3.07e9 if tiled else 4.54e9) if n_atoms == 25 else None
     res = {"kernel": "%s (fused -i H(t) psi, 2^%d full space, uniform drive + detuning + vdW diagonal)"
                      % ("apply_tiled_kernel x2 passes" if tiled else "apply_kernel", n_atoms),
            "bound": "hbm", "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],

@@ -23,7 +23,7 @@ LIB_PATH = os.path.join(_HERE, "libbqa_b200.so")
 
 EXPORTS = [
     "bqa_version", "bqa_last_error", "bqa_device_count", "bqa_set_device", "bqa_device_info",
-    "bqa_launch_count", "bqa_plan_create", "bqa_plan_destroy", "bqa_plan_set_stream",
+    "bqa_launch_count", "bqa_tiled_plan_describe", "bqa_plan_create", "bqa_plan_destroy", "bqa_plan_set_stream",
     "bqa_plan_add_diagonal", "bqa_plan_build_rydberg", "bqa_plan_get_diagonal", "bqa_plan_add_csr",
     "bqa_apply", "bqa_evolve_batch", "bqa_run_batch", "bqa_norm", "bqa_normalize", "bqa_expectation",
     "bqa_local_trace", "bqa_sample", "bqa_plan_enable_timing", "bqa_plan_get_timing",
@@ -103,6 +103,19 @@ def require_device():
 
 def launch_count() -> int:
     return int(load().bqa_launch_count())
+
+
+def tiled_plan_describe(n_local: int, n_total: int = None):
+    """pass list of the tiled H psi: dicts with lo_bits, hb, tb, p0, n_x, xbit, pair, pair_b (host arithmetic only)"""
+    import numpy as np
+
+    out = np.zeros((8, 8), dtype=np.int32)
+    n = load().bqa_tiled_plan_describe(c_int32(n_local), c_int32(n_local if n_total is None else n_total),
+                                       out.ctypes.data_as(c_void_p), c_int32(8))
+    if n < 0:
+        raise BackendError("bqa_tiled_plan_describe: bad shape")
+    keys = ("lo_bits", "hb", "tb", "p0", "n_x", "xbit", "pair", "pair_b")
+    return [dict(zip(keys, (int(v) for v in out[i]))) for i in range(n)]
 
 
 def _ptr(a) -> c_void_p:

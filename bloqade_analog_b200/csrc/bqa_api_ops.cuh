@@ -108,6 +108,8 @@ static bool tiled_plan(int n_loc, int n_total, int64_t rank, const cplx* const* 
       s.pair = 1;
       s.pair_b = s.xbit < s.hb ? s.xbit - s.lo_bits : (s.hb - s.lo_bits) + (s.xbit - (s.hb + s.tb));
     }
+    // L2 eviction hints (TileSpec::hint): on by default, measured 0.772 -> 0.760 ms and 3.30 -> 3.07 GB at 2^25
+    s.hint = getenv("BQA_TILED_HINT") ? atoi(getenv("BQA_TILED_HINT")) : 3;
     s.n_total = n_total;
     s.idx_hi = (long long)(rank << n_loc);
     s.raw = raw;
@@ -159,6 +161,21 @@ static int apply_tiled_launch(bqa_plan* p, const std::vector<TileSpec>& passes, 
 }
 
 extern "C" {
+
+int bqa_tiled_plan_describe(int32_t n_local, int32_t n_total, int32_t* out, int32_t max_passes) {
+  std::vector<TileSpec> passes;
+  const cplx* const peer = reinterpret_cast<const cplx*>(16);  // stands for "a peer shard": never dereferenced
+  const cplx* none[3] = {peer, peer, peer};
+  if (!out || n_total < n_local || n_total - n_local > 3) return -1;
+  if (!tiled_plan(n_local, n_total, 0, none, 0, passes)) return 0;
+  if ((int)passes.size() > max_passes) return -1;
+  for (size_t i = 0; i < passes.size(); ++i) {
+    const TileSpec& s = passes[i];
+    const int32_t row[8] = {s.lo_bits, s.hb, s.tb, s.first ? 0 : s.p0, s.n_x, s.xbit, s.pair, s.pair_b};
+    memcpy(out + 8 * i, row, sizeof(row));
+  }
+  return (int)passes.size();
+}
 
 int bqa_plan_add_csr(bqa_plan* p, int32_t amp_wf, int32_t phase_wf, int64_t nnz, const double* data,
                      const int32_t* indices, const int64_t* indptr) {

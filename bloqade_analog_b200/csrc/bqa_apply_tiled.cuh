@@ -42,6 +42,7 @@ struct TileSpec {
   int xbit;
   int pair;      // the leftover atom is local: tiles are walked in partner pairs (t, t ^ (1 << pair_b))
   int pair_b;    // bit of the TILE index that the leftover atom's index bit maps to
+  int hint;      // L2 eviction hints: bit 0 side streams and result stores evict_first, bit 1 psi tiles evict_last
   int first;     // first pass: out = (diag psi + flips); otherwise out += flips
   int last;      // last pass: multiply by -i unless raw
   int raw;
@@ -90,6 +91,34 @@ __device__ __forceinline__ double ldg_f64(const double* g) {
   double v;
   asm volatile("ld.global.nc.f64 %0, [%1];" : "=d"(v) : "l"(g));
   return v;
+}
+// The same accesses with an L2 eviction policy: the tile a CTA has just fetched is the leftover-atom partner of
+// the next one, so the streams that are touched once (V, partial result, stores) should not push it out of L2.
+__device__ __forceinline__ uint64_t l2_policy(int kind) {  // 0 normal, 1 evict_first, 2 evict_last
+  uint64_t pol;
+  if (kind == 1)
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  else if (kind == 2)
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  else
+    asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* g, uint64_t pol) {
+  asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(smem_addr), "l"(g), "l"(pol) : "memory");
+}
+__device__ __forceinline__ cplx ldg_cplx(const cplx* g, uint64_t pol) {
+  cplx z;
+  asm volatile("ld.global.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;" : "=d"(z.re), "=d"(z.im) : "l"(g), "l"(pol));
+  return z;
+}
+__device__ __forceinline__ double ldg_f64(const double* g, uint64_t pol) {
+  double v;
+  asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(g), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ void stg_cplx(cplx* g, double re, double im, uint64_t pol) {
+  asm volatile("st.global.L2::cache_hint.v2.f64 [%0], {%1, %2}, %3;" ::"l"(g), "d"(re), "d"(im), "l"(pol) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
@@ -149,6 +178,8 @@ __device__ __forceinline__ void apply_tiled_body(const int64_t dim, const int n,
   const uint32_t s_crp = sbase + (uint32_t)(kTileSlotBytes + offsetof(TileShared, crp));
   const uint32_t s_cip = sbase + (uint32_t)(kTileSlotBytes + offsetof(TileShared, cip));
   const uint32_t s_tabk = sbase + (uint32_t)(kTileSlotBytes + offsetof(TileShared, tabK));
+  const uint64_t pol_once = l2_policy((S.hint & 1) ? 1 : 0);  // V, partial result, stores: touched once per pass
+  const uint64_t pol_psi = l2_policy((S.hint & 2) ? 2 : 0);   // psi tiles: re-read as leftover-atom partners
   uint32_t s0 = 0;  // ring slot of amplitude k = 0 of the current tile (uniform over the CTA)
   // byte offset of the slot holding amplitude k of the current tile; k in [16, 32) addresses the next tile
   auto slot = [&](int k) -> uint32_t {
@@ -208,16 +239,16 @@ __device__ __forceinline__ void apply_tiled_body(const int64_t dim, const int n,
       for (int j = 0; j < kQuad; ++j) {
         const size_t off = (size_t)(g * kQuad + j) * stride;
         if (kFirst)
-          vq[j] = V ? ldg_f64(Vt + off) : 0.0;
+          vq[j] = V ? ldg_f64(Vt + off, pol_once) : 0.0;
         else
-          oq[j] = ldg_cplx(out_t + off);
-        if (kHasX) xq[j] = ldg_cplx(xsrc + off);
+          oq[j] = ldg_cplx(out_t + off, pol_once);
+        if (kHasX) xq[j] = ldg_cplx(xsrc + off, pol_psi);
       }
       // a quarter of the next tile per quad, behind the latency-critical side streams (the whole tile at once
       // is a 96 KB burst per SM that the side streams then queue behind)
       if (has_next) {
 #pragma unroll
-        for (int k = g * kQuad; k < (g + 1) * kQuad; ++k) cp_async16(smem0 + slot(kTilePer + k), nsrc + (size_t)k * stride);
+        for (int k = g * kQuad; k < (g + 1) * kQuad; ++k) cp_async16(smem0 + slot(kTilePer + k), nsrc + (size_t)k * stride, pol_psi);
         cp_async_commit();
       }
       cplx own[kQuad];
@@ -290,7 +321,7 @@ __device__ __forceinline__ void apply_tiled_body(const int64_t dim, const int n,
           ar[j] = fma(xr, xq[j].re, fma(-xi, xq[j].im, ar[j]));
           ai[j] = fma(xr, xq[j].im, fma(xi, xq[j].re, ai[j]));
         }
-        out_t[(size_t)(g * kQuad + j) * stride] = rot ? cmake(ai[j], -ar[j]) : cmake(ar[j], ai[j]);
+        stg_cplx(out_t + (size_t)(g * kQuad + j) * stride, rot ? ai[j] : ar[j], rot ? -ar[j] : ai[j], pol_once);
       }
     }
     if (!has_next) break;

@@ -84,6 +84,12 @@ int bqa_set_device(int32_t device);
 int bqa_device_info(int32_t* sm_count, int64_t* smem_per_block_optin, int64_t* l2_bytes);
 /* total kernel launches issued by this library since load (bench.py "gpu_launches") */
 int64_t bqa_launch_count(void);
+/* Pass list of the shared-memory-tiled H(t) psi (csrc/bqa_apply_tiled.cuh) for the n_local atoms a device holds
+ * of an n_total-atom two-level register (n_total > n_local: sharded state, rank 0).  Host arithmetic only - no
+ * GPU needed; the CPU test suite checks with it that every atom is flipped exactly once and every tile is
+ * visited exactly once.  passes[i][8] = {lo_bits, hb, tb, p0, n_x, xbit, pair, pair_b}.  Returns the number
+ * of passes (0: this shape is not tiled), or -1 when max_passes is too small. */
+int bqa_tiled_plan_describe(int32_t n_local, int32_t n_total, int32_t* passes, int32_t max_passes);
 
 /* ---- plan: structure shared by all tasks of a sweep ---------------------------------------------
  * replaces RydbergHamiltonianCodeGen.visit_register (emulate/codegen/hamiltonian.py:63-91) */
