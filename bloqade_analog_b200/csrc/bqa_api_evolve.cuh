@@ -166,13 +166,15 @@ static int evolve_small_device(bqa_plan* p, const double* d_records, const int64
   A.counter = d_counter;
   const int64_t dim = p->P.dim;
   int rc;
+  int threads = dim <= 256 ? 128 : (dim <= 1024 ? 256 : (dim <= 2048 ? 512 : 1024));
+  if (const char* e = getenv("BQA_SMALL_THREADS")) threads = atoi(e);  // measurement hook (profiles/r01_summary.md)
   if (use_cluster)
     rc = launch_cluster(p, A, n_tasks);
-  else if (dim <= 256)
+  else if (threads <= 128)
     rc = launch_small<128>(p, A, n_tasks);
-  else if (dim <= 1024)
+  else if (threads <= 256)
     rc = launch_small<256>(p, A, n_tasks);
-  else if (dim <= 2048)
+  else if (threads <= 512)
     rc = launch_small<512>(p, A, n_tasks);
   else
     rc = launch_small<1024>(p, A, n_tasks);
