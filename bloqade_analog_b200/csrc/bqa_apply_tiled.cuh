@@ -378,11 +378,6 @@ inline int tiled_variant(bool real, const TileSpec& s) {
 }
 
 // host: does any Rabi term of this task record carry a phase waveform?  (No: all coefficients are real.)
-inline bool record_has_phase(const double* rec_host) {
-  const TaskView tv = task_view(rec_host);
-  for (int k = 0; k < tv.n_rabi; ++k)
-    if ((int)tv.rabi[(int64_t)k * (3 + tv.n_atoms) + 1] >= 0) return true;
-  return false;
-}
+inline bool record_has_phase(const double* rec_host) { return task_has_phase(task_view(rec_host)); }
 
 }  // namespace bqa

@@ -50,6 +50,7 @@ struct ClusterIn {
 };
 
 struct ClusterCtx {
+  static constexpr bool kFastRhs = false;
   double* red;        // shared scratch [3 * 32]
   double* part;       // shared [2][4] cluster-exchange slots (double buffered)
   int parity;

@@ -121,6 +121,13 @@ BQA_HD TaskView task_view(const double* rec) {
   return tv;
 }
 
+// does any Rabi term of the task carry a phase waveform?  (No: every coefficient c[s][a] is real, c_im == 0 exactly.)
+BQA_HD bool task_has_phase(const TaskView& tv) {
+  for (int k = 0; k < tv.n_rabi; ++k)
+    if ((int)tv.rabi[(int64_t)k * (3 + tv.n_atoms) + 1] >= 0) return true;
+  return false;
+}
+
 BQA_HD int64_t task_record_size(const double* rec) {
   TaskView tv = task_view(rec);
   return (tv.rabi - rec) + (int64_t)tv.n_rabi * (3 + tv.n_atoms);

@@ -44,10 +44,16 @@ struct TaskEvolver {
   Workspace w;
   SolverOpts o;
   Controller c;
+  // two-level full space, no CSR term, Schroedinger picture, no phase waveform: contexts with kFastRhs evaluate
+  // the RHS with their own fused routine (same arithmetic in the same order, so the results are bit-identical)
+  bool fast_rhs;
 
   BQA_HD TaskEvolver(Ctx& ctx_, const PlanView& P_, const double* rec, const double* V_, Workspace w_,
                      SolverOpts o_)
-      : ctx(ctx_), P(P_), tv(task_view(rec)), V(V_), w(w_), o(o_) {}
+      : ctx(ctx_), P(P_), tv(task_view(rec)), V(V_), w(w_), o(o_) {
+    fast_rhs = P.full_space && P.n_level == 2 && P.n_csr == 0 && o.interaction == 0 && P.dim <= ((int64_t)1 << 30) &&
+               !task_has_phase(tv);
+  }
 
   BQA_HD cplx* y() const { return w.vec[kVecY]; }
   BQA_HD cplx* ys() const { return w.vec[kVecYs]; }
@@ -86,6 +92,13 @@ struct TaskEvolver {
     const auto in = ctx.gather(ys());
     const double* Vd = V;
     const bool inter = o.interaction != 0;
+    if constexpr (Ctx::kFastRhs) {
+      if (fast_rhs) {
+        ctx.rhs_full2_real(P.n_atoms, P.dim, cf, Vd, ys(), kout);
+        ctx.sync();
+        return;
+      }
+    }
     ctx.for_each(P.dim, [&](int64_t i) {
       cplx hz = h_apply_dispatch(Pr, cf, inter ? nullptr : Vd, in, i);
       if (inter && Vd) hz = cmul_conj_a(phase_u(Vd[i], t), hz);

@@ -17,7 +17,69 @@
 namespace bqa {
 
 struct CtaCtx {
+  static constexpr bool kFastRhs = true;
   double* red;  // shared scratch [3 * 32]
+
+  // kout = -i H(t) ys for a two-level full space with real coefficients (TaskEvolver::fast_rhs).  Same
+  // arithmetic in the same order as h_apply_element, so the result is bit-identical; what changes is the
+  // instruction count (ncu: the generic loop spends ~24 instructions per flip on 64-bit index arithmetic, a
+  // complex multiply by a real number and per-element coefficient loads).  A thread evaluates its (up to) four
+  // elements together: coefficients are read once per atom, partner indices are 32-bit XORs, and ys - always
+  // resident in shared memory for this engine - is read with ld.shared.
+  template <bool kShared>
+  __device__ __forceinline__ void rhs_full2_real_impl(int n, uint32_t dim, const Coefs& C, const double* __restrict__ V,
+                                                      const cplx* ys, cplx* kout) {
+    const uint32_t bd = blockDim.x;
+    const uint32_t sbase = kShared ? (uint32_t)__cvta_generic_to_shared(ys) : 0u;
+    auto load = [&](uint32_t idx) -> cplx {
+      if (kShared) {
+        cplx z;
+        asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(z.re), "=d"(z.im) : "r"(sbase + idx * 16u));
+        return z;
+      }
+      return ys[idx];
+    };
+    for (uint32_t i0 = threadIdx.x; i0 < dim; i0 += 4u * bd) {
+      double ar[4], ai[4], dg[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t i = i0 + (uint32_t)j * bd;
+        ar[j] = 0.0;
+        ai[j] = 0.0;
+        dg[j] = (V && i < dim) ? __ldg(V + i) : 0.0;
+      }
+#pragma unroll 2
+      for (int a = 0; a < n; ++a) {
+        const double cr = C.c_re[0][a], dl = C.delta[0][a];
+        const uint32_t bit = 1u << a;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t i = i0 + (uint32_t)j * bd;
+          if (i < dim) {
+            if (i & bit) dg[j] -= dl;
+            const cplx z = load(i ^ bit);
+            ar[j] += cr * z.re;
+            ai[j] += cr * z.im;
+          }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t i = i0 + (uint32_t)j * bd;
+        if (i < dim) {
+          const cplx zi = load(i);
+          kout[i] = times_minus_i(cmake(dg[j] * zi.re + ar[j], dg[j] * zi.im + ai[j]));
+        }
+      }
+    }
+  }
+  __device__ __forceinline__ void rhs_full2_real(int n, int64_t dim, const Coefs& C, const double* V, const cplx* ys,
+                                                 cplx* kout) {
+    if (__isShared(ys))
+      rhs_full2_real_impl<true>(n, (uint32_t)dim, C, V, ys, kout);
+    else
+      rhs_full2_real_impl<false>(n, (uint32_t)dim, C, V, ys, kout);
+  }
 
   template <class F>
   __device__ __forceinline__ void for_each(int64_t n, F f) {

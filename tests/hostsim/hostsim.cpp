@@ -16,6 +16,7 @@
 using namespace bqa;
 
 struct HostCtx {
+  static constexpr bool kFastRhs = false;
   template <class F>
   void for_each(int64_t n, F f) {
     for (int64_t i = 0; i < n; ++i) f(i);
