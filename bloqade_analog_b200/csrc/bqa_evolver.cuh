@@ -47,6 +47,8 @@ struct TaskEvolver {
   // two-level full space, no CSR term, Schroedinger picture, no phase waveform: contexts with kFastRhs evaluate
   // the RHS with their own fused routine (same arithmetic in the same order, so the results are bit-identical)
   bool fast_rhs;
+  bool coefs_ready = false;  // the shared coefficient scratch holds the values of time coefs_t
+  double coefs_t = 0.0;
 
   BQA_HD TaskEvolver(Ctx& ctx_, const PlanView& P_, const double* rec, const double* V_, Workspace w_,
                      SolverOpts o_)
@@ -69,7 +71,8 @@ struct TaskEvolver {
     });
   }
 
-  BQA_HD void eval_coefs(double t) {
+  // coefficients at time t into the shared scratch; visible after the caller's next barrier
+  BQA_HD void eval_coefs_nosync(double t) {
     int ne = tv.n_atoms * (P.n_level - 1);
     Coefs* cf = w.coefs;
     const TaskView& tvr = tv;
@@ -80,13 +83,18 @@ struct TaskEvolver {
       else
         coef_csr_entry(Pr, tvr, t, (int)(e - ne), *cf);
     });
+  }
+  BQA_HD void eval_coefs(double t) {
+    eval_coefs_nosync(t);
     ctx.sync_local();
   }
 
   // kout = f(t, .) evaluated on the stage input held in ys (already multiplied by u(t) in the
   // interaction picture)
   BQA_HD void rhs_from_ys(double t, cplx* kout) {
-    eval_coefs(t);
+    // stage_input(t, ...) has already evaluated the coefficients of this time (one barrier less per stage)
+    if (!(coefs_ready && coefs_t == t)) eval_coefs(t);
+    coefs_ready = false;
     const PlanView& Pr = P;
     const Coefs& cf = *w.coefs;
     const auto in = ctx.gather(ys());
@@ -109,6 +117,11 @@ struct TaskEvolver {
 
   // ys = (u(t) *) [ y + h * sum_j val[j] * K[slot[j]] ]     (nnz = 0: ys = (u(t)*) y)
   BQA_HD void stage_input(double t, double h, int nnz, const int* slot, const double* val) {
+    // the RHS that follows is evaluated at the same time t: its coefficients are computed here (the previous RHS
+    // is complete) and become visible with the barrier that ends this pass
+    eval_coefs_nosync(t);
+    coefs_t = t;
+    coefs_ready = true;
     cplx* out = ys();
     const cplx* yy = y();
     cplx* const* kk = w.vec + kVecK;
