@@ -127,6 +127,13 @@ struct TaskEvolver {
     cplx* const* kk = w.vec + kVecK;
     const double* Vd = V;
     const bool rot = rotating();
+    if constexpr (Ctx::kFastRhs) {
+      if (!rot) {  // same sums in the same order, four elements per thread and the term loop outermost
+        ctx.stage_input_plain(P.dim, h, nnz, slot, val, kk, yy, out);
+        ctx.sync();
+        return;
+      }
+    }
     ctx.for_each(P.dim, [&](int64_t i) {
       double sr = 0.0, si = 0.0;
       for (int j = 0; j < nnz; ++j) {

@@ -73,6 +73,39 @@ struct CtaCtx {
       }
     }
   }
+  // ys = y + h * sum_j val[j] * K[slot[j]] without the interaction-picture rotation: the (up to) four elements of a
+  // thread together, term loop outermost, so the vector pointer and the coefficient of a term are fetched once
+  // per thread and four independent loads are in flight per term.  Per element the sum runs over j in the same
+  // order as TaskEvolver::stage_input, so the result is bit-identical.
+  __device__ __forceinline__ void stage_input_plain(int64_t dim64, double h, int nnz, const int* slot, const double* val,
+                                                    cplx* const* kk, const cplx* yy, cplx* out) {
+    const uint32_t dim = (uint32_t)dim64, bd = blockDim.x;
+    for (uint32_t i0 = threadIdx.x; i0 < dim; i0 += 4u * bd) {
+      double sr[4] = {0.0, 0.0, 0.0, 0.0}, si[4] = {0.0, 0.0, 0.0, 0.0};
+      for (int j = 0; j < nnz; ++j) {
+        const cplx* kp = kk[slot[j]];
+        const double v = val[j];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const uint32_t i = i0 + (uint32_t)e * bd;
+          if (i < dim) {
+            const cplx kz = kp[i];
+            sr[e] += v * kz.re;
+            si[e] += v * kz.im;
+          }
+        }
+      }
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const uint32_t i = i0 + (uint32_t)e * bd;
+        if (i < dim) {
+          const cplx yz = yy[i];
+          out[i] = cmake(yz.re + h * sr[e], yz.im + h * si[e]);
+        }
+      }
+    }
+  }
+
   __device__ __forceinline__ void rhs_full2_real(int n, int64_t dim, const Coefs& C, const double* V, const cplx* ys,
                                                  cplx* kout) {
     if (__isShared(ys))
