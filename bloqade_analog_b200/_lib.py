@@ -28,7 +28,7 @@ EXPORTS = [
     "bqa_apply", "bqa_evolve_batch", "bqa_run_batch", "bqa_norm", "bqa_normalize", "bqa_expectation",
     "bqa_local_trace", "bqa_sample", "bqa_plan_enable_timing", "bqa_plan_get_timing",
     "bqa_shard_sync_bytes", "bqa_shard_alloc", "bqa_shard_open", "bqa_shard_close", "bqa_shard_free",
-    "bqa_plan_build_rydberg_shard", "bqa_apply_sharded", "bqa_evolve_sharded",
+    "bqa_plan_build_rydberg_shard", "bqa_apply_sharded", "bqa_evolve_sharded", "bqa_norm_noalloc",
 ]
 
 
@@ -291,6 +291,10 @@ class Plan:
         out = c_double(0.0)
         _check(load().bqa_norm(self._h, _ptr(psi), c_int32(mem), byref(out)))
         return out.value
+
+    def norm_noalloc(self, psi_dev: int, n_states: int, norm_dev: int):
+        """bqa_norm_noalloc: device pointers only, no allocation, no synchronisation (enqueued on the plan's stream)"""
+        _check(load().bqa_norm_noalloc(self._h, c_void_p(int(psi_dev)), c_int32(int(n_states)), c_void_p(int(norm_dev))))
 
     def normalize(self, psi, mem=MEM_HOST):
         _check(load().bqa_normalize(self._h, _ptr(psi), c_int32(mem)))

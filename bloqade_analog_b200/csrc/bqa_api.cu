@@ -307,3 +307,4 @@ int bqa_plan_get_diagonal(bqa_plan* p, int32_t id, double* v_host) {
 
 #include "bqa_api_ops.cuh"
 #include "bqa_api_shard.cuh"
+#include "bqa_api_noalloc.cuh"

@@ -167,6 +167,22 @@ int bqa_expectation(bqa_plan* plan, const double* record, int64_t record_len, do
 int bqa_local_trace(bqa_plan* plan, const void* psi, int32_t mem, int32_t n_sites, int32_t site_a, int32_t site_b,
                     const double* op, double* result);
 
+/* ---- allocation-free norm ------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same two
+ * deterministic passes as bqa_norm (StateVector.norm), but the per-CTA partial sums live in a file-scope
+ * `static __device__` array of BQA_NOALLOC_MAX_PARTIALS doubles (512 KiB, held by every GPU that loads the
+ * library until the process exits) instead of cudaMalloc'ed plan scratch.  The call allocates nothing, copies
+ * nothing to the host and does not synchronise: psi_dev[n_states][dim] and norm_dev[n_states] are DEVICE
+ * pointers owned by the caller, the two kernels are enqueued on the plan's stream and norm_dev[s] = ||psi_s||_2
+ * is valid once that stream reaches the end of the call's work.  The plan's device must be current.  Rejected
+ * with an error when n_states * (CTAs per state, at most 4 per SM) exceeds BQA_NOALLOC_MAX_PARTIALS.  All
+ * calls on one GPU share the array: calls that overlap on the GPU (different streams / threads) race; calls
+ * ordered on one stream do not.  Nothing has to start at zero (every slot read was written by the same call).
+ * The first call on a device looks the array's address up (cudaGetSymbolAddress): make it outside a capture. */
+#define BQA_NOALLOC_MAX_PARTIALS 65536
+int bqa_norm_noalloc(bqa_plan* plan, const void* psi_dev, int32_t n_states, double* norm_dev);
+
 /* ---- kernel (4): Born sampling (Space.sample_state_vector, space.py:211-229) ---------------------------
  * psi[n_states][dim] (normalised or not: the CDF is divided by its last element like np.random.choice),
  * uniforms[n_states][n_shots] -> shots[n_states][n_shots][n_atoms] */
