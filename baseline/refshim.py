@@ -1,9 +1,10 @@
-"""Import shim that loads the READ-ONLY reference (`/root/reference/src`) in the build container.
+"""Import shim that loads the UNMODIFIED reference package: `/root/reference/src` in the build container,
+else `baseline/_ref` (the copy `baseline/install_ref.py` makes; it travels to the GPU box).
 
-TEST TOOLING ONLY.  It is used by `tests/golden/make_golden.py` (golden-vector generation) and by
-the optional `-m "not gpu"` cross-checks that run only when `/root/reference` exists.  Nothing in the
-product package, `bench.py`, `smoke()` or the `-m gpu` tests imports this file; the reference does
-not exist on the GPU box.
+TEST / BASELINE TOOLING ONLY.  It is used by `tests/golden/make_golden.py` (golden-vector generation), by the
+drop-in tests (which need a real `bloqade.analog` to drive `program.bloqade.python().run(...)` on the B200
+routine and to compare it with the reference's own routine in the same process), and by `bench.py`'s
+reference arm and `.run()` end-to-end leg.  Nothing in the product package imports this file.
 
 The reference's hot path (emulate/*) never touches plotting / cloud SDKs, but `import bloqade.analog`
 pulls them in transitively.  They are absent from this image and there is no network, so they are
@@ -24,7 +25,10 @@ import os
 import sys
 import types
 
-REFERENCE_SRC = "/root/reference/src"
+_HERE = os.path.dirname(os.path.abspath(__file__))
+REFERENCE_SRC = os.environ.get("BQA_REFERENCE_SRC", "/root/reference/src")  # override: test the copy here
+if not os.path.isdir(os.path.join(REFERENCE_SRC, "bloqade", "analog")):
+    REFERENCE_SRC = os.path.join(_HERE, "_ref")
 
 
 def reference_available() -> bool:

@@ -28,7 +28,7 @@ EXPORTS = [
     "bqa_apply", "bqa_evolve_batch", "bqa_run_batch", "bqa_norm", "bqa_normalize", "bqa_expectation",
     "bqa_local_trace", "bqa_sample", "bqa_plan_enable_timing", "bqa_plan_get_timing",
     "bqa_shard_sync_bytes", "bqa_shard_alloc", "bqa_shard_open", "bqa_shard_close", "bqa_shard_free",
-    "bqa_plan_build_rydberg_shard", "bqa_apply_sharded", "bqa_evolve_sharded", "bqa_norm_noalloc",
+    "bqa_plan_build_rydberg_shard", "bqa_apply_sharded", "bqa_evolve_sharded", "bqa_norm_noalloc", "bqa_current_device",
 ]
 
 
@@ -93,6 +93,13 @@ def device_count() -> int:
         _check(load().bqa_device_count(byref(n)))
     except BackendError:
         return 0
+    return n.value
+
+
+def current_device() -> int:
+    """the CUDA device current in this thread"""
+    n = c_int32(0)
+    _check(load().bqa_current_device(byref(n)))
     return n.value
 
 

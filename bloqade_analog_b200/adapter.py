@@ -1,7 +1,7 @@
 """Bridge from a real `bloqade.analog` installation to the B200 backend IR.
 
 Only imported when `bloqade.analog` is importable (a user's environment, or the build container
-through tests/golden/refshim.py).  Converts the reference's `EmulatorProgram`
+through baseline/refshim.py).  Converts the reference's `EmulatorProgram`
 (`src/bloqade/analog/emulate/ir/emulator.py:241-246`) - register, per-coupling `Fields`, and the
 `JITWaveform`s - into `bloqade_analog_b200.ir`, node for node.  Waveforms are taken from
 `JITWaveform.canonicalized_ir` (emulator.py:32-63), i.e. after assignment and after `Sample`

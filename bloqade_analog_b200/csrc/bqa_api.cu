@@ -54,6 +54,21 @@ static void api_enter(const char* name) {
 }
 #define BQA_ENTER() api_enter(__func__)
 
+struct bqa_plan;
+static void api_enter_plan(const char* name, const bqa_plan* p);
+// entry points that take a plan make the plan's device current in the calling thread (one host thread per
+// GPU may drive plans of different devices concurrently)
+#define BQA_ENTER_PLAN(p) api_enter_plan(__func__, (p))
+
+// per-device "done once" flags (kernel attributes are per device)
+static bool once_per_device(std::atomic<uint64_t>& mask, bool set = false) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const uint64_t bit = 1ull << (dev & 63);
+  if (set) mask.fetch_or(bit);
+  return (mask.load() & bit) != 0;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // plan
 // ---------------------------------------------------------------------------------------------------
@@ -79,6 +94,14 @@ struct bqa_plan {
   double evolve_ms = 0.0;
   int64_t evolve_launches = 0;
 };
+
+static void api_enter_plan(const char* name, const bqa_plan* p) {
+  if (p) {
+    int cur = -1;
+    if (cudaGetDevice(&cur) != cudaSuccess || cur != p->device) cudaSetDevice(p->device);
+  }
+  api_enter(name);
+}
 
 static int plan_scratch(bqa_plan* p, size_t bytes, void** out) {
   if (bytes > p->scratch_bytes) {
@@ -162,6 +185,14 @@ int bqa_set_device(int32_t device) {
   return 0;
 }
 
+int bqa_current_device(int32_t* device) {
+  BQA_ENTER();
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  if (device) *device = dev;
+  return 0;
+}
+
 int bqa_device_info(int32_t* sm_count, int64_t* smem_per_block_optin, int64_t* l2_bytes) {
   BQA_ENTER();
   int dev = 0, v = 0;
@@ -239,7 +270,7 @@ void bqa_plan_destroy(bqa_plan* p) {
 }
 
 int bqa_plan_enable_timing(bqa_plan* p, int32_t on) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p) return fail("null plan");
   if (on && !p->ev0) {
     CK(cudaEventCreate(&p->ev0));
@@ -252,7 +283,7 @@ int bqa_plan_enable_timing(bqa_plan* p, int32_t on) {
 }
 
 int bqa_plan_get_timing(bqa_plan* p, double* evolve_kernel_ms, int64_t* evolve_kernel_launches) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p) return fail("null plan");
   if (evolve_kernel_ms) *evolve_kernel_ms = p->evolve_ms;
   if (evolve_kernel_launches) *evolve_kernel_launches = p->evolve_launches;
@@ -260,14 +291,14 @@ int bqa_plan_get_timing(bqa_plan* p, double* evolve_kernel_ms, int64_t* evolve_k
 }
 
 int bqa_plan_set_stream(bqa_plan* p, void* s) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p) return fail("null plan");
   p->stream = (cudaStream_t)s;
   return 0;
 }
 
 int bqa_plan_add_diagonal(bqa_plan* p, const double* v_host, int32_t* diag_id) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p || !v_host) return fail("bqa_plan_add_diagonal: null argument");
   double* d = nullptr;
   CK(cudaMalloc(&d, sizeof(double) * p->P.dim));
@@ -278,7 +309,7 @@ int bqa_plan_add_diagonal(bqa_plan* p, const double* v_host, int32_t* diag_id) {
 }
 
 int bqa_plan_build_rydberg(bqa_plan* p, const double* pair_host, int32_t* diag_id) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p || !pair_host) return fail("bqa_plan_build_rydberg: null argument");
   const int n = p->P.n_atoms;
   double *d = nullptr, *d_pair = nullptr;
@@ -297,7 +328,7 @@ int bqa_plan_build_rydberg(bqa_plan* p, const double* pair_host, int32_t* diag_i
 }
 
 int bqa_plan_get_diagonal(bqa_plan* p, int32_t id, double* v_host) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p || id < 0 || id >= (int)p->diags.size()) return fail("bqa_plan_get_diagonal: bad id");
   CK(cudaMemcpy(v_host, p->diags[id], sizeof(double) * p->P.dim, cudaMemcpyDeviceToHost));
   return 0;

@@ -223,7 +223,7 @@ extern "C" {
 int bqa_evolve_batch(bqa_plan* p, const double* records, const int64_t* offsets, int32_t n_tasks,
                      const bqa_solver_opts* o, const void* psi0, int32_t psi0_shared, const double* times,
                      int32_t n_times, void* psi_out, bqa_task_stats* stats, int32_t mem) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p || !records || !offsets || !times || n_tasks < 1 || n_times < 1) return fail("bqa_evolve_batch: bad argument");
   if (check_opts(o)) return 1;
   const int64_t dim = p->P.dim;
@@ -265,7 +265,7 @@ int bqa_evolve_batch(bqa_plan* p, const double* records, const int64_t* offsets,
 int bqa_run_batch(bqa_plan* p, const double* records, const int64_t* offsets, int32_t n_tasks,
                   const bqa_solver_opts* o, const double* times, const double* uniforms, int32_t n_shots,
                   int32_t project, uint8_t* shots, void* psi_out, bqa_task_stats* stats, int32_t mem) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p || !records || !offsets || !times || !uniforms || !shots || n_tasks < 1 || n_shots < 1)
     return fail("bqa_run_batch: bad argument");
   if (check_opts(o)) return 1;

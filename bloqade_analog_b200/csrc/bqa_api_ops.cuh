@@ -135,11 +135,11 @@ static TiledKernel tiled_kernel_for(bool real, const TileSpec& s) {
       K<R, false, true, 3>, K<R, true, false, 0>, K<R, true, true, 0>
   static const TiledKernel tab[16] = {BQA_TILED_VARIANTS(apply_tiled_kernel, false),
                                       BQA_TILED_VARIANTS(apply_tiled_kernel, true)};
-  static bool attr_set = false;
-  if (!attr_set) {
+  static std::atomic<uint64_t> attr_set{0};
+  if (!once_per_device(attr_set)) {
     for (TiledKernel k : tab)
       if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileDynSmem) != cudaSuccess) return nullptr;
-    attr_set = true;
+    once_per_device(attr_set, true);
   }
   return tab[tiled_variant(real, s)];
 }
@@ -179,7 +179,7 @@ int bqa_tiled_plan_describe(int32_t n_local, int32_t n_total, int32_t* out, int3
 
 int bqa_plan_add_csr(bqa_plan* p, int32_t amp_wf, int32_t phase_wf, int64_t nnz, const double* data,
                      const int32_t* indices, const int64_t* indptr) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p || !data || !indices || !indptr) return fail("bqa_plan_add_csr: null argument");
   if (p->csr.size() >= 8) return fail("bqa_plan_add_csr: at most 8 generic terms");
   const int64_t dim = p->P.dim;
@@ -224,7 +224,7 @@ int bqa_plan_add_csr(bqa_plan* p, int32_t amp_wf, int32_t phase_wf, int64_t nnz,
 
 int bqa_apply(bqa_plan* p, const double* record, int64_t record_len, double t, int32_t interaction, int32_t raw,
               const void* psi_in, void* psi_out, int32_t mem) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p || !record || !psi_in || !psi_out) return fail("bqa_apply: null argument");
   const int64_t dim = p->P.dim;
   Staged rec, in, out;
@@ -258,7 +258,7 @@ int bqa_apply(bqa_plan* p, const double* record, int64_t record_len, double t, i
 }
 
 int bqa_norm(bqa_plan* p, const void* psi, int32_t mem, double* norm) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p || !psi || !norm) return fail("bqa_norm: null argument");
   const int64_t dim = p->P.dim;
   Staged in;
@@ -276,7 +276,7 @@ int bqa_norm(bqa_plan* p, const void* psi, int32_t mem, double* norm) {
 }
 
 int bqa_normalize(bqa_plan* p, void* psi, int32_t mem) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p || !psi) return fail("bqa_normalize: null argument");
   const int64_t dim = p->P.dim;
   Staged buf;
@@ -297,7 +297,7 @@ int bqa_normalize(bqa_plan* p, void* psi, int32_t mem) {
 
 int bqa_expectation(bqa_plan* p, const double* record, int64_t record_len, double t, const void* psi, int32_t mem,
                     double* average, double* variance) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p || !record || !psi) return fail("bqa_expectation: null argument");
   const int64_t dim = p->P.dim;
   Staged rec, in;
@@ -327,7 +327,7 @@ int bqa_expectation(bqa_plan* p, const double* record, int64_t record_len, doubl
 
 int bqa_local_trace(bqa_plan* p, const void* psi, int32_t mem, int32_t n_sites, int32_t site_a, int32_t site_b,
                     const double* op, double* result) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p || !psi || !op || !result) return fail("bqa_local_trace: null argument");
   if (n_sites != 1 && n_sites != 2) return fail("bqa_local_trace: n_sites must be 1 or 2");
   if (site_a < 0 || site_a >= p->P.n_atoms || (n_sites == 2 && (site_b < 0 || site_b >= p->P.n_atoms)))
@@ -354,7 +354,7 @@ int bqa_local_trace(bqa_plan* p, const void* psi, int32_t mem, int32_t n_sites, 
 
 int bqa_sample(bqa_plan* p, const void* psi, int32_t n_states, const double* uniforms, int32_t n_shots,
                int32_t project, uint8_t* shots, int32_t mem) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p || !psi || !uniforms || !shots) return fail("bqa_sample: null argument");
   const int64_t dim = p->P.dim;
   Staged in, un, out;

@@ -83,7 +83,7 @@ int bqa_shard_free(void* dev_ptr) {
 }
 
 int bqa_plan_build_rydberg_shard(bqa_plan* p, int32_t n_total, const double* pair_host, int32_t rank, int32_t* diag_id) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p || !pair_host || !diag_id) return fail("bqa_plan_build_rydberg_shard: null argument");
   if (!p->P.full_space || p->P.n_level != 2 || n_total < p->P.n_atoms || n_total > 31)
     return fail("bqa_plan_build_rydberg_shard: two-level full space, n_total <= 31");
@@ -108,7 +108,7 @@ int bqa_plan_build_rydberg_shard(bqa_plan* p, int32_t n_total, const double* pai
 int bqa_apply_sharded(bqa_plan* p, const double* record, int64_t record_len, double t, int32_t raw,
                       int32_t n_atoms_total, int32_t rank, const void* const* partners, const void* psi_in,
                       void* psi_out) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!p || !record || !partners || !psi_in || !psi_out) return fail("bqa_apply_sharded: null argument");
   const int g = n_atoms_total - p->P.n_atoms;
   if (g < 1 || g > 3 || rank < 0 || rank >= (1 << g)) return fail("bqa_apply_sharded: bad shard geometry");
@@ -133,7 +133,7 @@ int bqa_apply_sharded(bqa_plan* p, const double* record, int64_t record_len, dou
 int bqa_evolve_sharded(bqa_plan* p, const double* record, int64_t record_len, const bqa_solver_opts* o,
                        const bqa_shard_desc* d, const void* psi0_local, const double* times, int32_t n_times,
                        void* psi_out_local, bqa_task_stats* stats) {
-  BQA_ENTER();
+  BQA_ENTER_PLAN(p);
   if (!record || !times || n_times < 1) return fail("bqa_evolve_sharded: bad argument");
   if (check_opts(o)) return 1;
   if (shard_check(p, d)) return 1;

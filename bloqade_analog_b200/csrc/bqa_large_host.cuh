@@ -120,11 +120,11 @@ static int evolve_large_device(bqa_plan* p, const double* d_records, const std::
   if (sh && !R.tiled)
     return fail("sharded evolve needs a two-level full space with >= 14 local atoms, no CSR term, Schroedinger picture");
   if (R.tiled) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static std::atomic<uint64_t> attr_set{0};
+    if (!once_per_device(attr_set)) {
       for (int v = 0; v < 16; ++v)
         CK(cudaFuncSetAttribute(lg_tiled_kernel_at(v), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileDynSmem));
-      attr_set = true;
+      once_per_device(attr_set, true);
     }
   }
   CK(cudaMalloc(&work, sizeof(cplx) * dim * n_vec));

@@ -27,6 +27,8 @@ class CompileCache:
 
     space_cache: Dict[Register, Tuple[Space, "_lib.Plan"]] = field(default_factory=dict)
     diagonal_cache: Dict[Tuple, int] = field(default_factory=dict)
+    # host-side Spaces, shareable between the caches of several devices (a Space has no device state)
+    shared_spaces: Dict[Register, Space] = field(default_factory=dict)
 
 
 class RydbergHamiltonianCodeGen:
@@ -36,11 +38,18 @@ class RydbergHamiltonianCodeGen:
         self.device = device
         self.device_diagonal_min_dim = device_diagonal_min_dim
 
+    def space_only(self, register: Register) -> Space:
+        """the Space of `register`, built once per CompileCache.shared_spaces (no device work)"""
+        spaces = self.compile_cache.shared_spaces
+        if register not in spaces:
+            spaces[register] = Space.create(register)
+        return spaces[register]
+
     def _space_and_plan(self, register: Register):
         cache = self.compile_cache.space_cache
         if register in cache:
             return cache[register]
-        space = Space.create(register)
+        space = self.space_only(register)
         plan = make_plan(space, self.device)
         cache[register] = (space, plan)
         return space, plan

@@ -27,12 +27,16 @@ from decimal import Decimal
 from enum import Enum
 from typing import Callable, Dict, List, Optional, Sequence, Tuple, Union
 
-Number = Union[int, float, Decimal]
+from .vecnum import DecVec, NonUniformSweep, tofloat as _flt
+
+Number = Union[int, float, Decimal, DecVec]
 
 
 def _dec(x: Number) -> Decimal:
-    """Same literal handling as the reference's scalar `cast` (Decimal(str(x)))."""
-    if isinstance(x, Decimal):
+    """Same literal handling as the reference's scalar `cast` (Decimal(str(x))).  A `DecVec` (one Decimal
+    per task of a sweep, vecnum.py) passes through: the lowering below is written so that it runs
+    unchanged on such vector numbers."""
+    if isinstance(x, (Decimal, DecVec)):
         return x
     return Decimal(str(x))
 
@@ -359,20 +363,22 @@ def flatten_waveform(wf: Waveform) -> List[Piece]:
 
         if isinstance(node, (Linear, Constant, Poly, PythonFn)):
             h = clip_hi(shift + node.duration)
-            flo = -math.inf if lo is None else float(lo)
+            flo = -math.inf if lo is None else _flt(lo)
             if lo is not None and h <= lo:
                 return
             if isinstance(node, Linear):
                 if node.duration.is_zero():
                     raise ValueError("Duration of linear waveform is zero. Cannot divide by zero.")
-                coeffs = (float(node.start), float((node.stop - node.start) / node.duration))
-                pieces.append(Piece(flo, float(h), float(shift), scale, coeffs))
+                coeffs = (_flt(node.start), _flt((node.stop - node.start) / node.duration))
+                pieces.append(Piece(flo, _flt(h), _flt(shift), scale, coeffs))
             elif isinstance(node, Constant):
-                pieces.append(Piece(flo, float(h), float(shift), scale, (float(node.value),)))
+                pieces.append(Piece(flo, _flt(h), _flt(shift), scale, (_flt(node.value),)))
             elif isinstance(node, Poly):
-                coeffs = tuple(float(c) for c in node.coeffs) or (0.0,)
-                pieces.append(Piece(flo, float(h), float(shift), scale, coeffs))
+                coeffs = tuple(_flt(c) for c in node.coeffs) or (0.0,)
+                pieces.append(Piece(flo, _flt(h), _flt(shift), scale, coeffs))
             else:
+                if isinstance(shift, DecVec) or isinstance(h, DecVec) or isinstance(node.duration, DecVec):
+                    raise NonUniformSweep("PythonFn waveforms are tabulated per task")
                 fshift = float(shift)
                 for (t0, t1, c) in _hermite_pieces(node.fn, float(node.duration), node.n_samples):
                     a = fshift + t0
@@ -382,8 +388,10 @@ def flatten_waveform(wf: Waveform) -> List[Piece]:
                     if phi > plo or (plo == -math.inf):
                         pieces.append(Piece(plo, phi, a, scale, c))
         elif hasattr(node, "pieces"):  # serialize.PieceTable: an already flattened table
+            if isinstance(shift, DecVec) or isinstance(hi, DecVec) or isinstance(lo, DecVec):
+                raise NonUniformSweep("piece tables are shifted per task")
             fshift = float(shift)
-            flo = -math.inf if lo is None else float(lo)
+            flo = -math.inf if lo is None else _flt(lo)
             for p in node.pieces:
                 plo = max(flo, p.lo + fshift) if p.lo != -math.inf else flo
                 phi = p.hi + fshift if hi is None else min(float(hi), p.hi + fshift)
@@ -404,7 +412,7 @@ def flatten_waveform(wf: Waveform) -> List[Piece]:
         elif isinstance(node, Negative):
             walk(node.waveform, shift, lo, hi, -scale)
         elif isinstance(node, Scale):
-            walk(node.waveform, shift, lo, hi, scale * float(node.scalar))
+            walk(node.waveform, shift, lo, hi, scale * _flt(node.scalar))
         elif isinstance(node, Add):
             walk(node.left, shift, lo, hi, scale)
             walk(node.right, shift, lo, hi, scale)

@@ -28,6 +28,7 @@ from .ir import (
     flatten_waveform,
 )
 from .space import Space
+from .vecnum import column, tofloat as _flt
 
 RB_C6 = 2 * np.pi * 862690  # rad um^6 / us   (reference constants.py:3)
 
@@ -85,28 +86,36 @@ class _WaveformTable:
         self.wf_start: List[int] = [0]
         self.pieces: List[List[float]] = []
         self.coefs: List[float] = []
-        self._ids: Dict[tuple, int] = {}
+        self._keys: List[Tuple[tuple, int]] = []
 
     def add(self, wf: Waveform, dedup: bool = True) -> int:
         flat = flatten_waveform(wf)
         key = tuple(flat)  # waveforms with identical piece tables share one entry
-        if dedup and key in self._ids:
-            return self._ids[key]
+        if dedup:
+            # compared entry by entry (not hashed): with the per-task vector numbers of a whole sweep (vecnum.py)
+            # tables that coincide for SOME tasks only must be noticed - the comparison raises NonUniformSweep
+            for other, wid in self._keys:
+                if len(other) == len(key) and other == key:
+                    return wid
         for p in flat:
             self.pieces.append([p.lo, p.hi, p.offset, p.scale, float(len(self.coefs)), float(len(p.coeffs))])
             self.coefs.extend(p.coeffs)
         self.wf_start.append(len(self.pieces))
         wid = len(self.wf_start) - 2
         if dedup:
-            self._ids[key] = wid
+            self._keys.append((key, wid))
         return wid
 
 
-def pack_task_record(program: EmulatorProgram, diag_id: int = 0,
-                     extra_waveforms: Sequence[Waveform] = ()) -> np.ndarray:
+def pack_task_record(program: EmulatorProgram, diag_id=0, extra_waveforms: Sequence[Waveform] = (),
+                     n_tasks: Optional[int] = None) -> np.ndarray:
     """Flatten the time-dependent part of one task into the float64 task record.
     `extra_waveforms` are appended to the waveform table (after the program's own, in order, without
-    de-duplication) for generic CSR terms registered with `bqa_plan_add_csr`."""
+    de-duplication) for generic CSR terms registered with `bqa_plan_add_csr`.
+
+    With `n_tasks`, `program` is a whole sweep whose numbers are per-task vectors (vecnum.py, built by
+    sweep.py) and `diag_id` may be an int array [n_tasks]: the result is records[n_tasks, L], row k
+    bit-identical to the record of task k lowered on its own."""
     reg = program.register
     n = len(reg)
     if n > MAX_ATOMS:
@@ -121,7 +130,7 @@ def pack_task_record(program: EmulatorProgram, diag_id: int = 0,
             w = table.add(term.amplitude)
             scale = [0.0] * n
             for atom, value in term.operator_data.target_atoms.items():
-                scale[atom] += float(value)
+                scale[atom] = scale[atom] + _flt(value)
             det_rows.append([float(w), float(slot)] + scale)
         for term in fields.rabi:
             w = table.add(term.amplitude)
@@ -132,13 +141,13 @@ def pack_task_record(program: EmulatorProgram, diag_id: int = 0,
                 raise ValueError("RabiAsymmetric term without a phase waveform")
             scale = [0.0] * n
             for atom, value in term.operator_data.target_atoms.items():
-                scale[atom] += float(value)
+                scale[atom] = scale[atom] + _flt(value)
             rabi_rows.append([float(w), float(pw), float(slot)] + scale)
     for wf in extra_waveforms:
         table.add(wf, dedup=False)
     header = [
-        float(program.duration),
-        float(diag_id),
+        program.duration if n_tasks is not None else float(program.duration),
+        diag_id if n_tasks is not None else float(diag_id),
         float(len(table.wf_start) - 1),
         float(len(table.pieces)),
         float(len(det_rows)),
@@ -154,7 +163,12 @@ def pack_task_record(program: EmulatorProgram, diag_id: int = 0,
         flat.extend(r)
     for r in rabi_rows:
         flat.extend(r)
-    return np.asarray(flat, dtype=np.float64)
+    if n_tasks is None:
+        return np.asarray(flat, dtype=np.float64)
+    out = np.empty((n_tasks, len(flat)), dtype=np.float64)
+    for j, x in enumerate(flat):
+        out[:, j] = x if isinstance(x, np.ndarray) else column(x, n_tasks)
+    return out
 
 
 def concat_records(records: Sequence[np.ndarray]) -> Tuple[np.ndarray, np.ndarray]:

@@ -15,6 +15,9 @@
  *     Plan descriptors, solver options, stats and scalar results are always host memory.
  *   - work is enqueued on the plan's stream (bqa_plan_set_stream, default stream 0) and the call
  *     returns after the stream is synchronised when any output is host memory.
+ *   - a plan belongs to the CUDA device that was current when it was created; every entry point that
+ *     takes a plan makes that device current in the calling thread, so one host thread per GPU can drive
+ *     plans of different devices concurrently (the routine's `devices=` sharding does).
  */
 #ifndef BQA_B200_H
 #define BQA_B200_H
@@ -81,6 +84,7 @@ int bqa_version(void);
 const char* bqa_last_error(void);
 int bqa_device_count(int32_t* count);
 int bqa_set_device(int32_t device);
+int bqa_current_device(int32_t* device);
 int bqa_device_info(int32_t* sm_count, int64_t* smem_per_block_optin, int64_t* l2_bytes);
 /* total kernel launches issued by this library since load (bench.py "gpu_launches") */
 int64_t bqa_launch_count(void);

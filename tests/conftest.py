@@ -111,6 +111,27 @@ def hostsim():
     return HostSim()
 
 
+def reference_available() -> bool:
+    """the UNMODIFIED reference package: /root/reference/src here, baseline/_ref on the GPU box"""
+    base = os.path.join(ROOT, "baseline")
+    if base not in sys.path:
+        sys.path.insert(0, base)
+    import refshim
+
+    return refshim.reference_available()
+
+
+def load_reference():
+    """import bloqade.analog (the reference) through baseline/refshim.py"""
+    assert reference_available()
+    import refshim
+
+    refshim.install()
+    import bloqade.analog
+
+    return bloqade.analog
+
+
 def cuda_available():
     try:
         from bloqade_analog_b200 import _lib
