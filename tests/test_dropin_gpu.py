@@ -100,7 +100,7 @@ def assert_same_batches(ref_batch, new_batch, max_diff_shots_per_task=1):
     assert type(new_batch).__mro__[-1] is object and isinstance(new_batch, type(ref_batch))
     assert list(new_batch.tasks.keys()) == list(ref_batch.tasks.keys())
     rr, rn = ref_batch.report(), new_batch.report()
-    assert type(rn) is type(rr)
+    assert isinstance(rn, type(rr))
     br, bn = rr.bitstrings(), rn.bitstrings()
     assert len(br) == len(bn)
     for a, b in zip(br, bn):
