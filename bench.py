@@ -12,11 +12,18 @@ data-path collective).
 
    python bench.py [--gpus N] [--steps K] [--warmup W] [--tasks T] [--impl reference]
 
-One JSON line on stdout (rank 0).  `value` = tasks/s with inputs resident in HBM; `e2e` = the same through
-the C ABI with pinned HOST buffers (H2D of records/uniforms and D2H of shots/stats inside the timed region);
-`roofline` = the dominant kernel of the step (the CTA-per-task evolve kernel); `roofline_hpsi` = the
-standalone fused H(t) psi apply on a BASELINE configs[3]-sized state (5x5 lattice, 2^25 amplitudes);
-`cpu_baseline` = the oracle's NumPy/SciPy/Numba port of the reference path on the host cores.
+One JSON line on stdout (rank 0).
+  value          tasks/s with inputs resident in HBM (device-timed, successful tasks only)
+  e2e            the same sweep through the call a user makes - program.bloqade.python().run(100) on the B200
+                 routine + batch.report() - lowering, H2D, GPU, D2H and packaging inside the timed region
+  e2e_c_abi      bqa_run_batch with pinned HOST buffers (the C-ABI level of the same step)
+  roofline       the dominant kernel of the step (the CTA-per-task evolve kernel)
+  roofline_hpsi  the standalone fused H(t) psi on a BASELINE configs[3]-sized state (5x5 lattice, 2^25 amplitudes)
+  cpu_baseline   the UNMODIFIED reference (baseline/_ref) on the host cores, bounded sample of the same sweep
+  strong         (N > 1) ONE 4096-task sweep split over the ranks
+  sharded        (N > 1) a (24 + log2 N)-atom state sharded over the ranks vs the unsharded run; N = 8: configs[4]
+  small_configs  configs[0] / configs[1] through .run()
+`--impl reference` runs the unmodified reference through its own API and parallel path on the host cores.
 """
 import argparse
 import json
@@ -48,23 +55,6 @@ def measured_peaks():
         with open(path) as f:
             return json.load(f), "measured"
     return {"hbm_gbs": 6650.0}, "fallback"
-
-
-def sweep_programs(n_tasks, rank=0):
-    """C3 sweep block of `rank`: 64 detunings x 64 durations (task = i_det * 64 + i_dur); other ranks get the
-    neighbouring block of final detunings (same spread of durations => same work per rank)."""
-    from bloqade_analog_b200 import programs
-
-    side = 64
-    dets = np.linspace(4.0, 32.0, side) + 0.2 * rank
-    durs = np.linspace(0.5, 4.0, side)
-    grid = [(float(round(d, 6)), float(round(t, 6))) for d in dets for t in durs]
-    if n_tasks < len(grid):  # sub-sampled sweep keeps the spread of durations
-        pick = np.linspace(0, len(grid) - 1, n_tasks).round().astype(int)
-        grid = [grid[i] for i in pick]
-    while len(grid) < n_tasks:
-        grid = grid + grid[: n_tasks - len(grid)]
-    return [programs.config3_task(d, t) for d, t in grid]
 
 
 # ------------------------------------------------------------------------------------------------------
@@ -121,80 +111,158 @@ class Clocks:
 
 
 # ------------------------------------------------------------------------------------------------------
-# CPU arm: the oracle port of the reference path (scipy.integrate.ode + per-term NumPy/Numba passes)
+# the reference itself (baseline/_ref on the GPU box, /root/reference in the build container)
 # ------------------------------------------------------------------------------------------------------
-def _cpu_task(args):
-    d, t, seed = args
+def load_reference():
+    """import the UNMODIFIED reference package through baseline/refshim.py; None when it is not present"""
+    base = os.path.join(ROOT, "baseline")
+    if base not in sys.path:
+        sys.path.insert(0, base)
+    try:
+        import refshim
+
+        if not refshim.reference_available():
+            return None
+        import warnings
+
+        warnings.filterwarnings("ignore")
+        refshim.install()
+        import bloqade.analog as ba
+
+        return ba
+    except Exception as e:  # noqa: BLE001
+        log("reference package unavailable:", repr(e))
+        return None
+
+
+def sweep_grid(n_tasks, rank=0):
+    """(final_detuning, total_duration) of the C3 sweep block of `rank`: 64 detunings x 64 durations (task =
+    i_det * 64 + i_dur); other ranks get the neighbouring block of final detunings (same spread of durations =>
+    same work per rank)."""
+    side = 64
+    dets = np.linspace(4.0, 32.0, side) + 0.2 * rank
+    durs = np.linspace(0.5, 4.0, side)
+    grid = [(float(round(d, 6)), float(round(t, 6))) for d in dets for t in durs]
+    if n_tasks < len(grid):  # sub-sampled sweep keeps the spread of durations
+        pick = np.linspace(0, len(grid) - 1, n_tasks).round().astype(int)
+        grid = [grid[i] for i in pick]
+    while len(grid) < n_tasks:
+        grid = grid + grid[: n_tasks - len(grid)]
+    return grid
+
+
+def sweep_programs(n_tasks, rank=0):
     from bloqade_analog_b200 import programs
-    from oracle import emulator as oe
 
-    prog = programs.config3_task(d, t)
-    rs = np.random.RandomState(seed)
-    t0 = time.perf_counter()
-    oe.run(prog, SHOTS, uniforms=rs.random_sample(SHOTS), **SOLVER)
-    return time.perf_counter() - t0
+    return [programs.config3_task(d, t) for d, t in sweep_grid(n_tasks, rank)]
 
 
-def _cpu_sample_grid(n):
+def builder_sweep(grid):
+    """the same sweep written with the reference's builder (what a user writes; README.md:88-108 waveforms):
+    Chain(12).rydberg...piecewise_linear([0.1, 0.8, 0.1] * total, ...).batch_assign(final_detuning=..., total=...)"""
+    from bloqade.analog import cast
+    from bloqade.analog.atom_arrangement import Chain
+
+    total = cast("total")
+    durations = [0.1 * total, 0.8 * total, 0.1 * total]
+    return (Chain(12, lattice_spacing=5.72).rydberg.rabi.amplitude.uniform.piecewise_linear(durations, [0, 15.8, 15.8, 0])
+            .detuning.uniform.piecewise_linear(durations, [-16.33, -16.33, "final_detuning", "final_detuning"])
+            .batch_assign(final_detuning=[g[0] for g in grid], total=[g[1] for g in grid]))
+
+
+REF_SAMPLE = 32  # tasks of one reference step: the same list on every box
+
+
+def reference_sample_grid(n=REF_SAMPLE):
     """n tasks spread over the sweep so that their mean duration equals the sweep's mean (2.25 us)"""
     side = 64
     dets = np.linspace(4.0, 32.0, side)
     durs = np.linspace(0.5, 4.0, side)
     idx = np.linspace(0, side - 1, n).round().astype(int)
-    return [(float(round(dets[(7 * k) % side], 6)), float(round(durs[i], 6)), k) for k, i in enumerate(idx)]
+    return [(float(round(dets[(7 * k) % side], 6)), float(round(durs[i], 6))) for k, i in enumerate(idx)]
 
 
-def cpu_warmup():
+def reference_run(ba, grid, workers):
+    """one pass of the UNMODIFIED reference over `grid` through its own public API and parallel path:
+    program.bloqade.python().run(100, multiprocessing=True, num_workers=workers)
+    (src/bloqade/analog/ir/routine/bloqade.py:233-311, task/batch.py:235-244)"""
+    routine = builder_sweep(grid).bloqade.python()
+    assert type(routine).__name__ == "BloqadePythonRoutine", "the reference arm must run the reference's own routine"
+    t0 = time.perf_counter()
+    if workers > 1:
+        batch = routine.run(SHOTS, multiprocessing=True, num_workers=workers, **SOLVER)
+    else:
+        batch = routine.run(SHOTS, **SOLVER)
+    dt = time.perf_counter() - t0
+    assert len(batch.tasks) == len(grid)
+    return dt
+
+
+def reference_versions():
+    import numba
+    import scipy
+
+    return f"scipy {scipy.__version__}, numba {numba.__version__}, numpy {np.__version__}"
+
+
+def cpu_baseline(n_sample, workers):
+    """bounded sample of the workload on the host cores: the reference itself when it is present, else the
+    oracle port on one core"""
+    ba = load_reference()
+    if ba is not None:
+        reference_run(ba, reference_sample_grid(2), 1)  # numba JIT + imports, untimed
+        grid = sorted(reference_sample_grid(n_sample), key=lambda g: -g[1])
+        dt = reference_run(ba, grid, workers)
+        return {"value": n_sample / dt, "unit": UNIT, "cores": workers, "kind": "reference",
+                "sample": f"{n_sample} of the 4096 sweep tasks (mean duration {np.mean([g[1] for g in grid]):.2f} us) through "
+                          f"the unmodified reference: program.bloqade.python().run(100, multiprocessing=True, "
+                          f"num_workers={workers}), {dt:.1f} s; {reference_versions()}; os.cpu_count()={os.cpu_count()}"}
     from bloqade_analog_b200 import programs
     from oracle import emulator as oe
 
     oe.run(programs.config3_task(8.0, 0.02), 4, uniforms=np.full(4, 0.5), **SOLVER)  # numba JIT
-
-
-def cpu_baseline_single(n_sample=3):
-    """rank-0 bounded sample on ONE core: tasks/s of the oracle port"""
-    cpu_warmup()
-    grid = _cpu_sample_grid(n_sample)
+    grid = reference_sample_grid(min(n_sample, 3))
     t0 = time.perf_counter()
-    for g in grid:
-        _cpu_task(g)
+    for d, t in grid:
+        oe.run(programs.config3_task(d, t), SHOTS, uniforms=np.random.RandomState(1).random_sample(SHOTS), **SOLVER)
     dt = time.perf_counter() - t0
-    return {"value": n_sample / dt, "unit": UNIT, "cores": 1, "kind": "port",
-            "sample": f"{n_sample} of the 4096 sweep tasks (durations {[g[1] for g in grid]} us), oracle/emulator.py "
-                      f"(scipy ode dop853 + numba term passes), {dt:.1f} s"}
+    return {"value": len(grid) / dt, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": f"{len(grid)} sweep tasks on oracle/emulator.py (reference package not present), {dt:.1f} s"}
+
+
+WORKLOAD = ("configs[2]: 4096-task detuning/duration sweep on a 12-atom chain (D=4096 full space), dop853 atol=1e-7 "
+            "rtol=1e-14, 100 shots/task")
 
 
 def reference_arm(args):
-    """`--impl reference`: the reference's CPU implementation of the path = the oracle port (the reference
-    itself is pure Python that cannot travel to the GPU box), on all host cores through a
-    process pool like the reference's own `multiprocessing=True` fan-out (task/batch.py:235-244)."""
+    """`--impl reference`: the UNMODIFIED reference (baseline/_ref) on the box's host cores through its own public
+    API and its own parallel path, on a bounded sample of the same workload (REF_SAMPLE tasks per step, the same
+    list on every box).  Rank 0 alone runs it."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import multiprocessing as mp
-
-    cores = os.cpu_count() or 1
-    workers = max(1, min(cores, 64))
-    per_step = 2 * workers  # bounded sample: two tasks per worker per step, longest first (~10 s steps)
-    grid = sorted(_cpu_sample_grid(per_step), key=lambda g: -g[1])
-    ctx = mp.get_context("fork")
-    cpu_warmup()
-    with ctx.Pool(workers) as pool:
-        for _ in range(max(1, min(args.warmup, 1))):
-            list(pool.imap_unordered(_cpu_task, grid[-workers:], chunksize=1))
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            list(pool.imap_unordered(_cpu_task, grid, chunksize=1))
-        dt = time.perf_counter() - t0
-    value = per_step * args.steps / dt
+    ba = load_reference()
+    if ba is None:
+        print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref (copy of the reference package) not present"}),
+              flush=True)
+        return
+    workers = max(1, min(os.cpu_count() or 1, REF_SAMPLE))
+    grid = sorted(reference_sample_grid(REF_SAMPLE), key=lambda g: -g[1])
+    reference_run(ba, reference_sample_grid(2), 1)  # numba JIT in this process; forked workers inherit it
+    for _ in range(max(0, min(args.warmup, 1))):
+        reference_run(ba, grid[-workers:], workers)
+    dts = [reference_run(ba, grid, workers) for _ in range(args.steps)]
+    dt = float(sum(dts))
+    value = REF_SAMPLE * args.steps / dt
+    sample = (f"{REF_SAMPLE} of the 4096 sweep tasks per step (spread over the sweep, mean duration "
+              f"{np.mean([g[1] for g in grid]):.2f} us = the sweep's mean), program.bloqade.python().run(100, "
+              f"multiprocessing=True, num_workers={workers}); {reference_versions()}; os.cpu_count()={os.cpu_count()}")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "configs[2]: 4096-task detuning/duration sweep, 12-atom chain (D=4096), dop853 atol=1e-7 rtol=1e-14, 100 shots",
-                   "sample_tasks_per_step": per_step},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": workers, "kind": "port",
-                         "sample": f"{per_step} sweep tasks per step over {workers} processes (oracle/emulator.py)"},
+        "config": {"workload": WORKLOAD, "sample_tasks_per_step": REF_SAMPLE, "api": "program.bloqade.python().run"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": workers, "kind": "reference", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -204,6 +272,15 @@ def reference_arm(args):
 # ------------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------------
+def profile_record(name):
+    """a number measured under ncu and committed under profiles/ (bench.py never runs under a profiler)"""
+    path = os.path.join(ROOT, "profiles", name)
+    if os.path.exists(path):
+        with open(path) as f:
+            return json.load(f)
+    return None
+
+
 def hpsi_roofline(torch, device_index, peaks, peak_kind, n_atoms=25, reps=20):
     """standalone fused H(t) psi on the C4-sized full space: algorithmic bytes 32*D per apply"""
     from bloqade_analog_b200 import _lib, ir, programs
@@ -232,17 +309,138 @@ def hpsi_roofline(torch, device_index, peaks, peak_kind, n_atoms=25, reps=20):
     alg = 32.0 * dim
     ach = alg / (np.median(ms) * 1e-3) / 1e9
     tiled = n_atoms > 13 and not os.environ.get("BQA_NO_TILED")
-    # ncu --set full, 2^25: dram read+write of the two tiled passes (profiles/r01_summary.md: 1.39 GB + 1.67 GB);
-    # one-pass gather kernel 4.54 GB
-    traffic = (3.07e9 if tiled else 4.54e9) if n_atoms == 25 else None
+    rec = profile_record("hpsi_traffic.json") or {}
+    traffic = rec.get("tiled" if tiled else "one_pass", {}).get(str(n_atoms))
     res = {"kernel": "%s (fused -i H(t) psi, 2^%d full space, uniform drive + detuning + vdW diagonal)"
-                     % ("apply_tiled_kernel x2 passes" if tiled else "apply_kernel", n_atoms),
+                     % ("apply_tiled_kernel passes" if tiled else "apply_kernel", n_atoms),
            "bound": "hbm", "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
            "frac_of_8TBps_nominal": ach / 8000.0, "peak_kind": peak_kind + " burst copy", "algorithmic_bytes_per_launch": alg,
-           "ms_per_launch_median": float(np.median(ms)), "ms_per_launch_min": float(ms.min()), "traffic": traffic}
+           "ms_per_launch_median": float(np.median(ms)), "ms_per_launch_min": float(ms.min()),
+           "traffic": traffic["bytes"] if traffic else None, "traffic_source": traffic["source"] if traffic else None}
     h.plan.close()
     del psi, out
     torch.cuda.empty_cache()
+    return res
+
+
+def small_config_lines(torch, ba, device):
+    """BASELINE configs[0] (C1, 6 tasks, 3x3 lattice) and configs[1] (C2, Chain(16) blockade subspace, D=2584)
+    end to end through program.bloqade.python().run(100) on the B200 routine: seconds per call"""
+    from bloqade.analog.atom_arrangement import Chain, Square
+
+    from bloqade_analog_b200 import routine
+
+    om, de, du = [0, 15.8, 15.8, 0], [-16.33, -16.33, 16.33, 16.33], [0.4, 3.2, 0.4]
+    c1 = (Square(3, lattice_spacing="a").rydberg.rabi.amplitude.uniform.piecewise_linear(du, om)
+          .detuning.uniform.piecewise_linear(du, de).batch_assign(a=list(np.arange(4.0, 7.0, 0.5))))
+    c2 = (Chain(16, lattice_spacing=5.72).rydberg.rabi.amplitude.uniform.piecewise_linear(du, om)
+          .detuning.uniform.piecewise_linear(du, de))
+    out = {}
+    for name, prog, kw in (("config1", c1, {}), ("config2a", c2, {"blockade_radius": 6.0})):
+        r = routine.b200_routine(prog)
+        r.run(SHOTS, devices=[device], **kw, **SOLVER)
+        ts = []
+        for _ in range(3):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            batch = r.run(SHOTS, devices=[device], **kw, **SOLVER)
+            ts.append(time.perf_counter() - t0)
+        n = len(batch.tasks)
+        st = [t.integrator_stats for t in batch.tasks.values()]
+        out[name] = {"tasks": n, "s_per_run_call": float(np.median(ts)), "tasks_per_s": n / float(np.median(ts)),
+                     "rhs_evals": int(sum(int(s["nfcn"]) for s in st)), "lowering": routine.LAST_LOWERING}
+    return out
+
+
+def sharded_leg(torch, dist, rank, world, local_rank):
+    """SURVEY.md 8(e) row 3 on the N GPUs of this run: a (24 + log2 N)-atom full-space state sharded over the ranks
+    against the unsharded run on rank 0 (H psi, dop853 evolution, sampling) + timings; at N = 8 also the
+    30-atom BASELINE configs[4] H psi."""
+    from bloqade_analog_b200 import _lib, ir, programs
+    from bloqade_analog_b200.hamiltonian import RydbergHamiltonianCodeGen
+    from bloqade_analog_b200.sharded import ShardedHamiltonian
+    from bloqade_analog_b200.state_vector import AnalogGate
+
+    g = int(np.log2(world))
+    n_atoms = 24 + g
+    dev = torch.device("cuda", local_rank)
+    d = 0.02
+    prog = programs.adiabatic_program(ir.chain_sites(n_atoms, lattice_spacing=5.5), durations=[0.1 * d, 0.8 * d, 0.1 * d])
+    sh = ShardedHamiltonian(prog)
+    ldim = sh.local_dim
+    res = {"n_atoms": n_atoms, "world": world, "local_dim": ldim, "duration_us": d}
+    full = RydbergHamiltonianCodeGen(device=local_rank).emit(prog) if rank == 0 else None
+    gen = torch.Generator(device="cpu").manual_seed(11)
+    psi_full = torch.randn(1 << n_atoms, 2, dtype=torch.float64, generator=gen)
+    psi_full /= psi_full.norm()
+    psi_loc = torch.view_as_complex(psi_full[rank * ldim:(rank + 1) * ldim].contiguous()).to(dev)
+    out = sh.apply(psi_loc, 0.6 * d, raw=True)
+    out_r = torch.view_as_real(out)
+    gathered = [torch.empty_like(out_r) for _ in range(world)] if rank == 0 else None
+    dist.gather(out_r, gathered, dst=0)
+    if rank == 0:
+        pf = psi_full.to(dev)
+        ref = torch.empty_like(pf)
+        full.plan.apply(full.record, 0.6 * d, pf.data_ptr(), ref.data_ptr(), raw=True, mem=_lib.MEM_DEVICE)
+        torch.cuda.synchronize()
+        got = torch.cat(gathered)
+        res["apply_max_rel_err"] = float((got - ref).abs().max() / ref.abs().max())
+        del pf, ref, got, gathered
+    del psi_full
+    partners = [sh.desc.ys[rank ^ (1 << b)] for b in range(sh.g)]
+
+    def time_apply(shh, n_total, reps=10):
+        part = [shh.desc.ys[rank ^ (1 << b)] for b in range(shh.g)]
+        o = torch.empty(shh.local_dim, dtype=torch.complex128, device=dev)
+        dist.barrier()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            shh.plan.apply_sharded(shh.record, 0.6 * d, n_total, rank, part, shh._ys, o.data_ptr(), raw=True)
+        b.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([a.elapsed_time(b) / reps], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t)
+
+    res["apply_ms"] = time_apply(sh, n_atoms)
+    res["apply_alg_GBps_per_gpu"] = 32.0 * (1 << n_atoms) / (res["apply_ms"] * 1e-3) / 1e9 / world
+    dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    states, stats = sh.evolve()
+    torch.cuda.synchronize()
+    res["evolve_s"] = time.perf_counter() - t0
+    res["stats"] = {k: int(stats[k][0]) for k in ("status", "nfcn", "nstep", "naccpt", "nrejct")}
+    res["ms_per_rhs"] = 1e3 * res["evolve_s"] / max(1, res["stats"]["nfcn"])
+    res["norm"] = sh.norm(states[0])
+    final_r = torch.view_as_real(states[0])
+    gathered = [torch.empty_like(final_r) for _ in range(world)] if rank == 0 else None
+    dist.gather(final_r, gathered, dst=0)
+    np.random.seed(9123892)
+    shots = sh.sample(states[0], 200)
+    if rank == 0:
+        (ref_state,) = AnalogGate(full).apply(full.space.zero_state(np.complex128), engine="streamed")
+        got = np.ascontiguousarray(torch.cat(gathered).cpu().numpy()).view(np.complex128).reshape(-1)
+        ov = np.vdot(ref_state.data, got)
+        res["infidelity"] = float(abs(1.0 - abs(ov) ** 2 / (np.vdot(got, got).real * np.vdot(ref_state.data, ref_state.data).real)))
+        np.random.seed(9123892)
+        ref_shots = full.plan.sample(got, np.random.random_sample(200))[0]
+        res["shots_rows_differing"] = int((ref_shots != shots).any(axis=1).sum())
+        full.plan.close()
+    sh.close()
+    del states, gathered
+    torch.cuda.empty_cache()
+    if world == 8:  # BASELINE configs[4]: 6x5 lattice, 2^30 amplitudes, 2 GiB per vector per GPU
+        prog5 = programs.config5()
+        sh5 = ShardedHamiltonian(prog5)
+        ms = time_apply(sh5, 30, reps=5)
+        res["config5_hpsi_ms"] = ms
+        res["config5_alg_GBps_per_gpu"] = 32.0 * (1 << 30) / (ms * 1e-3) / 1e9 / 8
+        res["config5_nvlink_floor_ms"] = 3 * (16.0 * (1 << 27)) / 900e9 * 1e3
+        sh5.close()
+    dist.barrier()
     return res
 
 
@@ -266,7 +464,7 @@ def gpu_arm(args):
     _lib.require_device()  # no CPU fallback: fails loudly without the CUDA library / a device
     peaks, peak_kind = measured_peaks()
 
-    # ---- host-side lowering (outside the timed region: done once per sweep, like _compile RB:204-231) ----
+    # ---- host-side lowering of the device-resident leg (outside its timed region) -----------------------
     t0 = time.perf_counter()
     progs = sweep_programs(args.tasks, rank)
     codegen = RydbergHamiltonianCodeGen(CompileCache(), device=local_rank)
@@ -295,14 +493,14 @@ def gpu_arm(args):
     d_times = torch.from_numpy(times).cuda()
     d_uni = torch.from_numpy(uniforms).cuda()
     d_shots = torch.empty((args.tasks, SHOTS, n_atoms), dtype=torch.uint8, device="cuda")
-    # pinned host inputs / outputs for the end-to-end leg
+    # pinned host inputs / outputs for the C-ABI host-buffer leg
     keep = [pinned(blob), pinned(offsets), pinned(times), pinned(uniforms)]
     h_blob, h_off, h_times, h_uni = (k[1] for k in keep)
     h_shots_t = torch.empty((args.tasks, SHOTS, n_atoms), dtype=torch.uint8).pin_memory()
     h_shots = h_shots_t.numpy()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
-    D, H = _lib.MEM_DEVICE, _lib.MEM_HOST
+    D = _lib.MEM_DEVICE
     last_stats = {}
 
     def step_device():
@@ -318,6 +516,12 @@ def gpu_arm(args):
         if dist is not None:
             dist.barrier()
         torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
 
     def timed(step_fn, steps, warmup):
         for _ in range(warmup):
@@ -336,25 +540,95 @@ def gpu_arm(args):
             b.synchronize()
             total_ms += a.elapsed_time(b)
         barrier()
-        t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
-        if dist is not None:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item()), _lib.launch_count() - launches0
+        return max_over_ranks(total_ms), _lib.launch_count() - launches0
 
     clocks = Clocks(local_rank) if rank == 0 else None
     dev_ms, launches = timed(step_device, args.steps, args.warmup)
     kern_ms, kern_n = plan.get_timing()
     st = last_stats["st"]
-    bad = int((st["status"] != 1).sum())
+    ok_tasks = int((st["status"] == 1).sum())
+    bad = args.tasks - ok_tasks
+    bad_ids = [int(i) for i in np.nonzero(st["status"] != 1)[0][:8]]
     nfcn_total = int(st["nfcn"].sum())
     clock_rec = clocks.stop() if clocks else None
-    e2e_ms, _ = timed(step_host, args.steps, 1)
-    st_h = last_stats["st"]
-    bad += int((st_h["status"] != 1).sum())
+    abi_ms, _ = timed(step_host, max(1, min(args.steps, 2)), 1)
+    abi_steps = max(1, min(args.steps, 2))
 
-    total_tasks = args.tasks * world
+    # ---- end to end through the call a user makes: program.bloqade.python().run(100) on the B200 routine ----
+    # timed region = everything .run() does for the rank's whole sweep: lowering of the symbolic program, drawing
+    # the sampling uniforms, H2D of records/uniforms, the GPU work, D2H of shots/stats, packaging into the
+    # reference's LocalBatch - plus batch.report() (the device->host result the user reads)
+    ba = load_reference()
+    e2e = None
+    if ba is not None:
+        from bloqade_analog_b200 import routine as b200_routine
+
+        grid = sweep_grid(args.tasks, rank)
+        routine = b200_routine.b200_routine(builder_sweep(grid))
+        parts = {}
+
+        def step_run():
+            t0 = time.perf_counter()
+            np.random.seed(9123892 + rank)
+            batch = routine.run(SHOTS, devices=[local_rank], raise_on_error=False, **SOLVER)
+            t1 = time.perf_counter()
+            rep = batch.report()
+            t2 = time.perf_counter()
+            parts["run_s"], parts["report_s"] = t1 - t0, t2 - t1
+            parts["rows"] = len(rep.dataframe)
+            parts["ok"] = sum(int(t.integrator_stats["status"]) == 1 for t in batch.tasks.values())
+            return batch
+
+        step_run()  # warm-up (imports, kernels)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step_run()
+        torch.cuda.synchronize()
+        run_s = max_over_ranks(time.perf_counter() - t0)
+        barrier()
+        e2e = {"value": parts["ok"] * world * args.steps / run_s, "unit": UNIT,
+               "h2d_bytes_per_step": int(blob.nbytes + offsets.nbytes + times.nbytes + uniforms.nbytes),
+               "d2h_bytes_per_step": int(h_shots.nbytes + st.nbytes), "ms_per_step": 1e3 * run_s / args.steps,
+               "api": "program.bloqade.python().run(100, ...) on BloqadeB200Routine + batch.report()",
+               "lowering": b200_routine.LAST_LOWERING, "run_call_s": parts["run_s"], "report_s": parts["report_s"],
+               "report_rows": parts["rows"], "timing": "host wall clock around the call, max over ranks"}
+    ok_h = int((last_stats["st"]["status"] == 1).sum())
+    abi = {"value": ok_h * world * abi_steps / (abi_ms * 1e-3), "unit": UNIT, "ms_per_step": abi_ms / abi_steps,
+           "api": "bqa_run_batch with pinned host buffers (C ABI)"}
+    if e2e is None:
+        e2e = dict(abi, h2d_bytes_per_step=int(blob.nbytes + offsets.nbytes + times.nbytes + uniforms.nbytes),
+                   d2h_bytes_per_step=int(h_shots.nbytes + st.nbytes), note="reference package absent: C-ABI level only")
+
+    # ---- strong scaling: ONE 4096-task sweep split over the ranks (distributed.run_programs_sharded) ---------
+    strong = None
+    if dist is not None and not args.no_strong:
+        from bloqade_analog_b200.distributed import run_programs_sharded
+
+        all_progs = sweep_programs(4096, 0)
+        u = np.random.RandomState(7).random_sample((4096, SHOTS))
+        run_programs_sharded(all_progs[: 64 * world], SHOTS, uniforms=u[: 64 * world], device=local_rank, **SOLVER)
+        barrier()
+        t0 = time.perf_counter()
+        res = run_programs_sharded(all_progs, SHOTS, uniforms=u, device=local_rank, **SOLVER)
+        torch.cuda.synchronize()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        strong = {"tasks_total": 4096, "value": sum(r.status == 1 for r in res) / dt, "unit": UNIT, "s": dt,
+                  "scaling": "strong", "note": "contiguous blocks of 4096/N tasks per rank incl. host lowering of the "
+                  "rank's block and the all_gather of shots"}
+
+    # ---- sharded full-space state over the N GPUs ---------------------------------------------------------
+    sharded = None
+    if dist is not None and not args.no_sharded:
+        del d_blob, d_uni, d_shots, flush
+        torch.cuda.empty_cache()
+        try:
+            sharded = sharded_leg(torch, dist, rank, world, local_rank)
+        except Exception as e:  # noqa: BLE001
+            sharded = {"error": repr(e)}
+
+    total_tasks = ok_tasks * world
     value = total_tasks * args.steps / (dev_ms * 1e-3)
-    e2e = total_tasks * args.steps / (e2e_ms * 1e-3)
 
     if rank != 0:
         if dist is not None:
@@ -366,13 +640,18 @@ def gpu_arm(args):
     alg_bytes = 32.0 * dim * nfcn_total  # 32*D per H psi x RHS evaluations of the launch
     kms = kern_ms / max(1, kern_n)
     ach = alg_bytes / (kms * 1e-3) / 1e9
+    evo = profile_record("evolve_kernel_ncu.json") or {}
     roofline = {
         "kernel": "evolve_small_kernel (CTA-per-task DOP853: all stage combines, fused H(t) psi and error norms)",
         "bound": "hbm", "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
-        "peak_kind": peak_kind + " copy bandwidth", "traffic": None,
+        "peak_kind": peak_kind + " copy bandwidth", "traffic": evo.get("dram_bytes_per_bench_launch"),
+        "traffic_source": evo.get("source"),
         "algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": kms, "share_of_step": kern_ms / dev_ms,
         "rhs_evals_per_launch": nfcn_total,
-        "note": "state vectors live in shared memory / L2, so the effective rate may exceed the HBM roofline",
+        "binding_resource": evo.get("binding_resource"),
+        "note": "the state vectors of a task live in shared memory / L2, so HBM is not the binding resource of this "
+                "kernel: 'achieved' is the algorithmic H psi rate (32*D per RHS) it sustains, 'binding_resource' the "
+                "pipe utilisation ncu measured (profiles/)",
     }
     hpsi = None
     if not args.no_hpsi:
@@ -380,29 +659,41 @@ def gpu_arm(args):
             hpsi = hpsi_roofline(torch, local_rank, peaks, peak_kind, args.hpsi_atoms)
         except Exception as e:  # noqa: BLE001
             hpsi = {"error": repr(e)}
-    cpu = None
-    if world == 1 or True:
+    small = None
+    if ba is not None and not args.no_small:
         try:
-            cpu = cpu_baseline_single(args.cpu_tasks)
+            small = small_config_lines(torch, ba, local_rank)
         except Exception as e:  # noqa: BLE001
-            cpu = {"error": repr(e)}
+            small = {"error": repr(e)}
+    cpu = None
+    try:
+        cores = max(1, min(os.cpu_count() or 1, 32))
+        cpu = cpu_baseline(args.cpu_tasks if args.cpu_tasks > 0 else 2 * cores, cores)
+    except Exception as e:  # noqa: BLE001
+        cpu = {"error": repr(e)}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "configs[2]: 4096-task detuning/duration sweep on a 12-atom chain (D=4096 full space), "
-                               "dop853 atol=1e-7 rtol=1e-14, 100 shots/task",
+        "config": {"workload": WORKLOAD,
                    "tasks_per_gpu": args.tasks, "engine": args.engine, "dim": dim, "shots": SHOTS, "parallelism": f"task-sharded x{world}, no collective",
                    "l2": "flushed between timed steps (256 MiB write)", "host_lowering_s": round(lower_s, 3),
-                   "failed_tasks": bad, "mean_rhs_per_task": nfcn_total / args.tasks},
-        "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int(blob.nbytes + offsets.nbytes + times.nbytes + uniforms.nbytes),
-                "d2h_bytes_per_step": int(h_shots.nbytes + st_h.nbytes), "ms_per_step": e2e_ms / args.steps},
+                   "failed_tasks": bad, "failed_task_ids": bad_ids, "value_counts": "successful tasks only",
+                   "mean_rhs_per_task": nfcn_total / args.tasks},
+        "e2e": e2e,
+        "e2e_c_abi": abi,
         "gpu_launches": int(launches),
         "roofline": roofline,
         "roofline_hpsi": hpsi,
         "cpu_baseline": cpu,
         "clocks": clock_rec,
     }
+    if strong is not None:
+        line["strong"] = strong
+    if sharded is not None:
+        line["sharded"] = sharded
+    if small is not None:
+        line["small_configs"] = small
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()
@@ -416,7 +707,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--tasks", type=int, default=4096, help="sweep tasks per GPU")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--cpu-tasks", type=int, default=3, help="tasks of the bounded CPU-baseline sample")
+    ap.add_argument("--cpu-tasks", type=int, default=0, help="tasks of the bounded CPU-baseline sample (0: 2 per core)")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (N > 1)")
+    ap.add_argument("--no-sharded", action="store_true", help="skip the sharded-state leg (N > 1)")
+    ap.add_argument("--no-small", action="store_true", help="skip the configs[0]/configs[1] lines")
     ap.add_argument("--hpsi-atoms", type=int, default=25)
     ap.add_argument("--no-hpsi", action="store_true")
     ap.add_argument("--engine", default="auto", choices=["auto", "cluster", "cta", "streamed"])

@@ -75,8 +75,12 @@ def config3_grid(n_detuning: int = 64, n_duration: int = 64):
 
 def config3_task(final_detuning: float, total: float, n_atoms: int = 12) -> ir.EmulatorProgram:
     """one C3 task: `Chain(12, lattice_spacing=5.72)`, Omega ramps 0 -> 15.8 -> 0 over
-    [0.1, 0.8, 0.1] * total, detuning -16.33 -> final_detuning"""
-    durations = [round(0.1 * total, 6), round(0.8 * total, 6), round(0.1 * total, 6)]
+    [0.1, 0.8, 0.1] * total, detuning -16.33 -> final_detuning.  The durations are the Decimal products the
+    reference builder forms for `[0.1 * total, 0.8 * total, 0.1 * total]` with `total = cast("total")`
+    (ir/scalar.py:528-529), so the record equals the one `program.bloqade.python()` lowers for the same
+    `batch_assign(final_detuning=..., total=...)` point bit for bit (tests/test_sweep_lowering.py)."""
+    t = ir._dec(total)
+    durations = [Decimal("0.1") * t, Decimal("0.8") * t, Decimal("0.1") * t]
     delta = [-16.33, -16.33, final_detuning, final_detuning]
     return adiabatic_program(ir.chain_sites(n_atoms, 5.72), durations, README_OMEGA, delta)
 

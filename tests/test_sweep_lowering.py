@@ -70,6 +70,12 @@ def test_config3_detuning_duration_sweep(ba):
     grid = [(float(round(d, 6)), float(round(t, 6))) for d in dets for t in durs]
     fast, slow = both(prog.batch_assign(final=[g[0] for g in grid], total=[g[1] for g in grid]))
     assert_identical(fast, slow)
+    # and the records equal the ones of the stand-alone program builder that bench.py and the GPU tests use
+    from bloqade_analog_b200 import lowering, programs
+
+    for k in (0, 77, 143):
+        want = lowering.pack_task_record(programs.config3_task(*grid[k]), 0)
+        assert np.array_equal(want.view(np.uint64), fast.records[k].view(np.uint64))
 
 
 def test_blockade_subspace_varying_positions_split_into_spaces(ba):
