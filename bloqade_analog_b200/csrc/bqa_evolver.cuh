@@ -30,9 +30,16 @@ constexpr int kVecYs = 1;
 constexpr int kVecK = 2;
 constexpr int kNumVec = 12;
 
+constexpr int kCoefTab = 11;  // stage times of one DOP853 step after the first stage (c2 h ... c11 h, h)
+
 struct Workspace {
   cplx** vec;     // [kNumVec] pointer table (shared)
   Coefs* coefs;   // shared scratch for the per-call coefficients
+  // optional (contexts with room for it): coefficient tables of ALL stage times of the current step,
+  // evaluated in one pass at the start of the step (step_coefs) instead of one serial evaluation in front of
+  // every stage - ncu showed the whole CTA waiting at the stage barrier for the one warp that evaluates the
+  // waveforms (19 % of the stall samples of evolve_small_kernel).  nullptr: evaluate per stage.
+  Coefs* coefs_tab = nullptr;
 };
 
 template <class Ctx>
@@ -49,6 +56,7 @@ struct TaskEvolver {
   bool fast_rhs;
   bool coefs_ready = false;  // the shared coefficient scratch holds the values of time coefs_t
   double coefs_t = 0.0;
+  int tab_n = 0;             // entries of w.coefs_tab valid for the current step
 
   BQA_HD TaskEvolver(Ctx& ctx_, const PlanView& P_, const double* rec, const double* V_, Workspace w_,
                      SolverOpts o_)
@@ -89,14 +97,38 @@ struct TaskEvolver {
     ctx.sync_local();
   }
 
+  // coefficient tables of the stage times  time_of(0) ... time_of(n-1)  of the step that starts now, all in one
+  // pass (one table entry per thread).  Same function of the same time values as eval_coefs: identical numbers.
+  template <class TimeOf>
+  BQA_HD void step_coefs(int n, TimeOf time_of) {
+    tab_n = 0;
+    if (w.coefs_tab == nullptr) return;
+    const int ne = tv.n_atoms * (P.n_level - 1), per = ne + P.n_csr;
+    Coefs* tab = w.coefs_tab;
+    const TaskView& tvr = tv;
+    const PlanView& Pr = P;
+    ctx.for_small((int64_t)n * per, [&](int64_t q) {
+      const int j = (int)(q / per), e = (int)(q - (int64_t)j * per);
+      const double t = time_of(j);
+      if (e < ne)
+        coef_entry(tvr, t, e, tab[j]);
+      else
+        coef_csr_entry(Pr, tvr, t, e - ne, tab[j]);
+    });
+    ctx.sync_local();
+    tab_n = n;
+  }
+  BQA_HD const Coefs* tab_entry(int idx) const { return (idx >= 0 && idx < tab_n) ? w.coefs_tab + idx : nullptr; }
+
   // kout = f(t, .) evaluated on the stage input held in ys (already multiplied by u(t) in the
   // interaction picture)
-  BQA_HD void rhs_from_ys(double t, cplx* kout) {
-    // stage_input(t, ...) has already evaluated the coefficients of this time (one barrier less per stage)
-    if (!(coefs_ready && coefs_t == t)) eval_coefs(t);
+  BQA_HD void rhs_from_ys(double t, cplx* kout, int tab = -1) {
+    const Coefs* pre = tab_entry(tab);  // evaluated by step_coefs at the start of the step
+    // otherwise stage_input(t, ...) has already evaluated the coefficients of this time (one barrier less per stage)
+    if (pre == nullptr && !(coefs_ready && coefs_t == t)) eval_coefs(t);
     coefs_ready = false;
     const PlanView& Pr = P;
-    const Coefs& cf = *w.coefs;
+    const Coefs& cf = pre ? *pre : *w.coefs;
     const auto in = ctx.gather(ys());
     const double* Vd = V;
     const bool inter = o.interaction != 0;
@@ -116,12 +148,14 @@ struct TaskEvolver {
   }
 
   // ys = (u(t) *) [ y + h * sum_j val[j] * K[slot[j]] ]     (nnz = 0: ys = (u(t)*) y)
-  BQA_HD void stage_input(double t, double h, int nnz, const int* slot, const double* val) {
+  BQA_HD void stage_input(double t, double h, int nnz, const int* slot, const double* val, int tab = -1) {
     // the RHS that follows is evaluated at the same time t: its coefficients are computed here (the previous RHS
-    // is complete) and become visible with the barrier that ends this pass
-    eval_coefs_nosync(t);
-    coefs_t = t;
-    coefs_ready = true;
+    // is complete) and become visible with the barrier that ends this pass - unless step_coefs has them already
+    if (tab_entry(tab) == nullptr) {
+      eval_coefs_nosync(t);
+      coefs_t = t;
+      coefs_ready = true;
+    }
     cplx* out = ys();
     const cplx* yy = y();
     cplx* const* kk = w.vec + kVecK;

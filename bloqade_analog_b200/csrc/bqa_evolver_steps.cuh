@@ -10,10 +10,12 @@ template <class Ctx>
 BQA_HD void TaskEvolver<Ctx>::step_dopri5(int& accepted) {
   const double x = c.x, h = c.h, tn = x + h;
   const int64_t n_real = 2 * P.dim;
+  auto stage_time = [=](int s) { return (s == 5) ? tn : x + tables::DOPRI5_c[s + 1] * h; };
+  step_coefs(6, stage_time);  // entries 0..4: stages 2..6, entry 5: the FSAL evaluation at x + h
   for (int s = 0; s < 5; ++s) {
-    double ts = x + tables::DOPRI5_c[s + 1] * h;
-    stage_input(ts, h, tables::DOPRI5_a_nnz[s], tables::DOPRI5_a_slot[s], tables::DOPRI5_a_val[s]);
-    rhs_from_ys(ts, k(s + 1));
+    double ts = stage_time(s);
+    stage_input(ts, h, tables::DOPRI5_a_nnz[s], tables::DOPRI5_a_slot[s], tables::DOPRI5_a_val[s], s);
+    rhs_from_ys(ts, k(s + 1), s);
   }
   double err = 0.0, stden = 0.0, stnum = 0.0;
   {
@@ -45,7 +47,7 @@ BQA_HD void TaskEvolver<Ctx>::step_dopri5(int& accepted) {
     });
     ctx.sync();
   }
-  rhs_from_ys(tn, k(1));  // k7 (FSAL), evaluated before the error test like Hairer's DOPRI5
+  rhs_from_ys(tn, k(1), 5);  // k7 (FSAL), evaluated before the error test like Hairer's DOPRI5
   {
     const cplx* yy = y();
     cplx* const* kk = w.vec + kVecK;
@@ -90,11 +92,13 @@ template <class Ctx>
 BQA_HD void TaskEvolver<Ctx>::step_dop853(int& accepted) {
   const double x = c.x, h = c.h, tn = x + h;
   const int64_t n_real = 2 * P.dim;
+  auto stage_time = [=](int s) { return (s == 10) ? tn : x + tables::DOP853_c[s + 1] * h; };
+  step_coefs(kCoefTab, stage_time);  // entry s = coefficients of stage s + 2; entry 10 (time x + h) also serves K4
   for (int s = 0; s < 11; ++s) {
-    double ts = (s == 10) ? tn : x + tables::DOP853_c[s + 1] * h;
-    stage_input(ts, h, tables::DOP853_a_nnz[s], tables::DOP853_a_slot[s], tables::DOP853_a_val[s]);
+    double ts = stage_time(s);
+    stage_input(ts, h, tables::DOP853_a_nnz[s], tables::DOP853_a_slot[s], tables::DOP853_a_val[s], s);
     int dst = (s == 9) ? 1 : (s == 10) ? 2 : s + 1;
-    rhs_from_ys(ts, k(dst));
+    rhs_from_ys(ts, k(dst), s);
   }
   c.nfcn += 11;
   double err = 0.0, err3 = 0.0, stden = 0.0;
@@ -115,7 +119,14 @@ BQA_HD void TaskEvolver<Ctx>::step_dop853(int& accepted) {
     const int* e3s = tables::DOP853_e3_slot[0];
     const double* e3v = tables::DOP853_e3_val[0];
     const double atol = o.atol, rtol = o.rtol;
-    ctx.for_each(P.dim, [&](int64_t i) {
+    bool done = false;
+    if constexpr (Ctx::kFastRhs) {
+      if (!rot && ctx.exact_dim(P.dim)) {  // same sums in the same order, four elements per thread
+        ctx.final853_exact(h, atol, rtol, kk, yy, ynew, out, err, err3, stden);
+        done = true;
+      }
+    }
+    if (!done) ctx.for_each(P.dim, [&](int64_t i) {
       double sr = 0.0, si = 0.0, e5r = 0.0, e5i = 0.0, e3r = 0.0, e3i = 0.0;
       for (int j = 0; j < bn; ++j) {
         cplx kz = kk[bs[j]][i];
@@ -155,7 +166,7 @@ BQA_HD void TaskEvolver<Ctx>::step_dop853(int& accepted) {
   ctx.sum3(err, err3, stden);
   accepted = c.decide(o, c.err_dop853(err, err3, n_real));
   if (accepted) {
-    rhs_from_ys(tn, k(3));  // K4 = f(x+h, ynew): next step's k1
+    rhs_from_ys(tn, k(3), 10);  // K4 = f(x+h, ynew): next step's k1
     c.nfcn += 1;
     if (c.stiff_due(o)) {
       const cplx* k4 = k(3);

@@ -16,9 +16,141 @@
 
 namespace bqa {
 
-struct CtaCtx {
+constexpr int ilog2_ct(int v) { return v <= 1 ? 0 : 1 + ilog2_ct(v / 2); }
+
+// kT: the CTA size when it is known at compile time (0: not known).  With dim == 4 * kT every thread owns exactly
+// the four elements tid + j * kT and the hot loops below have "exact" forms without bounds checks, with the
+// atom loop unrolled and the bit masks as immediates.
+template <int kT>
+struct CtaCtxT {
   static constexpr bool kFastRhs = true;
+  static constexpr int kLog = ilog2_ct(kT);
   double* red;  // shared scratch [3 * 32]
+
+  // ---- exact forms (dim == 4 * kT, two-level full space of kLog + 2 atoms) ----------------------------------
+  // Same arithmetic per element in the same order as the generic forms below => bit-identical results.  What
+  // changes is the instruction count: ncu (profiles/r02_summary.md) showed 17 instructions per bit flip in the
+  // generic loop (bounds branch, shift, index multiply, an unconditional subtract + two selects for the
+  // diagonal); here a flip is 1 LOP3 (shared by the thread's four elements) + LDS.128 + 2 DMUL + 2 DADD, and the
+  // diagonal subtract is predicated on the thread-index bit (warp-uniform for atoms >= 5) or known at compile time.
+  __device__ __forceinline__ void rhs_exact(const Coefs& C, const double* __restrict__ V, const cplx* ys, cplx* kout) {
+    constexpr int N = kLog + 2;
+    const uint32_t tid = threadIdx.x;
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(ys);
+    const uint32_t toff = tid * 16u;
+    auto load = [&](uint32_t byte_off) -> cplx {
+      cplx z;
+      asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(z.re), "=d"(z.im) : "r"(sbase + byte_off));
+      return z;
+    };
+    double ar[4] = {0.0, 0.0, 0.0, 0.0}, ai[4] = {0.0, 0.0, 0.0, 0.0}, dg[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) dg[j] = V ? __ldg(V + tid + (uint32_t)j * kT) : 0.0;
+#pragma unroll
+    for (int a = 0; a < N; ++a) {
+      const double cr = C.c_re[0][a], dl = C.delta[0][a];
+      if (a < kLog) {
+        if ((tid >> a) & 1u) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) dg[j] -= dl;
+        }
+        const uint32_t poff = toff ^ (16u << a);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const cplx z = load(poff + (uint32_t)j * (kT * 16u));
+          ar[j] += cr * z.re;
+          ai[j] += cr * z.im;
+        }
+      } else {
+        const int jb = 1 << (a - kLog);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (j & jb) dg[j] -= dl;
+          const cplx z = load(toff + (uint32_t)(j ^ jb) * (kT * 16u));
+          ar[j] += cr * z.re;
+          ai[j] += cr * z.im;
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const cplx zi = load(toff + (uint32_t)j * (kT * 16u));
+      kout[tid + (uint32_t)j * kT] = times_minus_i(cmake(dg[j] * zi.re + ar[j], dg[j] * zi.im + ai[j]));
+    }
+  }
+
+  __device__ __forceinline__ void stage_input_exact(double h, int nnz, const int* slot, const double* val,
+                                                    cplx* const* kk, const cplx* yy, cplx* out) {
+    const uint32_t tid = threadIdx.x;
+    double sr[4] = {0.0, 0.0, 0.0, 0.0}, si[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int j = 0; j < nnz; ++j) {
+      const cplx* kp = kk[slot[j]] + tid;
+      const double v = val[j];
+      cplx kz[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) kz[e] = kp[e * kT];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        sr[e] += v * kz[e].re;
+        si[e] += v * kz[e].im;
+      }
+    }
+    const cplx* yp = yy + tid;
+    cplx* op = out + tid;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const cplx yz = yp[e * kT];
+      op[e * kT] = cmake(yz.re + h * sr[e], yz.im + h * si[e]);
+    }
+  }
+
+  // new solution + both error estimators + stiffness denominator of a DOP853 step (step_dop853's final pass,
+  // Schroedinger picture), four elements per thread with the term loops outermost.  The per-thread partial sums
+  // err / err3 / stden accumulate element by element in the order of the generic loop (re before im).
+  __device__ __forceinline__ void final853_exact(double h, double atol, double rtol, cplx* const* kk, const cplx* yy,
+                                                 cplx* ynew, cplx* ys_io, double& err, double& err3, double& stden) {
+    const uint32_t tid = threadIdx.x;
+    double sr[4] = {0.0, 0.0, 0.0, 0.0}, si[4] = {0.0, 0.0, 0.0, 0.0};
+    double e5r[4] = {0.0, 0.0, 0.0, 0.0}, e5i[4] = {0.0, 0.0, 0.0, 0.0};
+    double e3r[4] = {0.0, 0.0, 0.0, 0.0}, e3i[4] = {0.0, 0.0, 0.0, 0.0};
+    auto accumulate = [&](int n, const int* slot, const double* val, double* accr, double* acci) {
+      for (int j = 0; j < n; ++j) {
+        const cplx* kp = kk[slot[j]] + tid;
+        const double v = val[j];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const cplx kz = kp[e * kT];
+          accr[e] += v * kz.re;
+          acci[e] += v * kz.im;
+        }
+      }
+    };
+    accumulate(tables::DOP853_b_nnz[0], tables::DOP853_b_slot[0], tables::DOP853_b_val[0], sr, si);
+    accumulate(tables::DOP853_e5_nnz[0], tables::DOP853_e5_slot[0], tables::DOP853_e5_val[0], e5r, e5i);
+    accumulate(tables::DOP853_e3_nnz[0], tables::DOP853_e3_slot[0], tables::DOP853_e3_val[0], e3r, e3i);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const uint32_t i = tid + (uint32_t)e * kT;
+      const cplx yo = yy[i];
+      const cplx z = cmake(yo.re + h * sr[e], yo.im + h * si[e]);
+      double sk = atol + rtol * fmax(fabs(yo.re), fabs(z.re));
+      double q = e5r[e] / sk;
+      err += q * q;
+      q = e3r[e] / sk;
+      err3 += q * q;
+      sk = atol + rtol * fmax(fabs(yo.im), fabs(z.im));
+      q = e5i[e] / sk;
+      err += q * q;
+      q = e3i[e] / sk;
+      err3 += q * q;
+      ynew[i] = z;
+      const cplx old = ys_io[i];
+      const double dr = z.re - old.re, di = z.im - old.im;
+      stden += dr * dr + di * di;
+      ys_io[i] = z;
+    }
+  }
+  __device__ __forceinline__ bool exact_dim(int64_t dim) const { return kT > 0 && dim == 4 * (int64_t)kT; }
 
   // kout = -i H(t) ys for a two-level full space with real coefficients (TaskEvolver::fast_rhs).  Same
   // arithmetic in the same order as h_apply_element, so the result is bit-identical; what changes is the
@@ -79,6 +211,10 @@ struct CtaCtx {
   // order as TaskEvolver::stage_input, so the result is bit-identical.
   __device__ __forceinline__ void stage_input_plain(int64_t dim64, double h, int nnz, const int* slot, const double* val,
                                                     cplx* const* kk, const cplx* yy, cplx* out) {
+    if (exact_dim(dim64)) {
+      stage_input_exact(h, nnz, slot, val, kk, yy, out);
+      return;
+    }
     const uint32_t dim = (uint32_t)dim64, bd = blockDim.x;
     for (uint32_t i0 = threadIdx.x; i0 < dim; i0 += 4u * bd) {
       double sr[4] = {0.0, 0.0, 0.0, 0.0}, si[4] = {0.0, 0.0, 0.0, 0.0};
@@ -108,7 +244,9 @@ struct CtaCtx {
 
   __device__ __forceinline__ void rhs_full2_real(int n, int64_t dim, const Coefs& C, const double* V, const cplx* ys,
                                                  cplx* kout) {
-    if (__isShared(ys))
+    if (exact_dim(dim) && n == kLog + 2 && __isShared(ys))
+      rhs_exact(C, V, ys, kout);
+    else if (__isShared(ys))
       rhs_full2_real_impl<true>(n, (uint32_t)dim, C, V, ys, kout);
     else
       rhs_full2_real_impl<false>(n, (uint32_t)dim, C, V, ys, kout);
@@ -175,6 +313,10 @@ struct CtaCtx {
   }
 };
 
+using CtaCtx = CtaCtxT<0>;
+
+constexpr int kSmallRecDoubles = 512;
+
 struct SmallArgs {
   PlanView P;
   const double* const* diags;   // device array of static-diagonal pointers (indexed by record diag_id)
@@ -202,11 +344,13 @@ template <int kThreads>
 __global__ void __launch_bounds__(kThreads, 1) evolve_small_kernel(const SmallArgs A) {
   extern __shared__ __align__(16) unsigned char dyn_smem[];
   __shared__ Coefs s_coefs;
+  __shared__ Coefs s_tab[kCoefTab];           // coefficients of all stage times of the current step
+  __shared__ double s_rec[kSmallRecDoubles];  // the task record (waveform pieces, scales) when it is small
   __shared__ double s_red[3 * 32];
   __shared__ cplx* s_vec[kNumVec];
   __shared__ int s_task;
 
-  CtaCtx ctx;
+  CtaCtxT<kThreads> ctx;
   ctx.red = s_red;
   const int64_t dim = A.P.dim;
   cplx* smem_vecs = reinterpret_cast<cplx*>(dyn_smem);
@@ -219,6 +363,14 @@ __global__ void __launch_bounds__(kThreads, 1) evolve_small_kernel(const SmallAr
     if (q >= A.n_tasks) break;
     const int task = A.order ? A.order[q] : q;
     const double* rec = A.records + A.offsets[task];
+    {
+      // waveform evaluation walks the record with dependent loads: keep it in shared memory (L2 latency otherwise)
+      const int64_t len = A.offsets[task + 1] - A.offsets[task];
+      if (len <= kSmallRecDoubles) {
+        for (int64_t i = threadIdx.x; i < len; i += kThreads) s_rec[i] = rec[i];
+        rec = s_rec;
+      }
+    }
 
     // (re)build the vector table: ranks < n_smem_vecs in shared memory, the rest in the workspace
     if (threadIdx.x == 0) {
@@ -246,7 +398,8 @@ __global__ void __launch_bounds__(kThreads, 1) evolve_small_kernel(const SmallAr
     Workspace w;
     w.vec = s_vec;
     w.coefs = &s_coefs;
-    TaskEvolver<CtaCtx> ev(ctx, A.P, rec, V, w, A.o);
+    w.coefs_tab = s_tab;
+    TaskEvolver<CtaCtxT<kThreads>> ev(ctx, A.P, rec, V, w, A.o);
 
     double t_cur = 0.0;
     bool failed = false;
