@@ -14,14 +14,16 @@ static const int kOrder853[kNumVec] = {kVecYs, kVecK + 0, kVecK + 3, kVecK + 4, 
 static const int kOrder5[kNumVec] = {kVecYs, kVecK + 0, kVecK + 1, kVecY, kVecK + 6, kVecK + 2,
                                      kVecK + 3, kVecK + 4, kVecK + 5, kVecK + 7, kVecK + 8, kVecK + 9};
 
-template <int kThreads>
+template <int kThreads, int kMinCtas = 1>
 static int launch_small(bqa_plan* p, SmallArgs& A, int n_tasks) {
-  auto kern = evolve_small_kernel<kThreads>;
+  auto kern = evolve_small_kernel<kThreads, kMinCtas>;
   cudaFuncAttributes fa;
   CK(cudaFuncGetAttributes(&fa, kern));
   const int64_t vec_bytes = (int64_t)sizeof(cplx) * A.P.dim;
   const int64_t dyn_max = p->smem_optin - (int64_t)fa.sharedSizeBytes - 1024;
   int n_smem = (int)std::min<int64_t>(A.n_vec, dyn_max / vec_bytes);
+  if (kMinCtas > 1)  // several CTAs (tasks) per SM: each one's share of the shared memory
+    n_smem = (int)std::min<int64_t>(A.n_vec, (p->smem_optin / kMinCtas - (int64_t)fa.sharedSizeBytes - 1024) / vec_bytes);
   if (n_smem < 0) n_smem = 0;
   // tiny states: leave room for several CTAs per SM instead of hoarding shared memory
   size_t dyn = (size_t)n_smem * vec_bytes;
@@ -166,10 +168,15 @@ static int evolve_small_device(bqa_plan* p, const double* d_records, const int64
   A.counter = d_counter;
   const int64_t dim = p->P.dim;
   int rc;
-  int threads = dim <= 256 ? 128 : (dim <= 1024 ? 256 : (dim <= 2048 ? 512 : 1024));
+  // measured at dim 4096 (profiles/r02_summary.md): 512 threads x 8 elements with 128 registers per thread keep more
+  // K-vector loads in flight than 1024 x 4 with 64 (75 vs 89 ms on the 148-task profile case); 256 x 16: 86 ms
+  int threads = dim <= 256 ? 128 : (dim <= 1024 ? 256 : (dim <= 4096 ? 512 : 1024));
   if (const char* e = getenv("BQA_SMALL_THREADS")) threads = atoi(e);  // measurement hook (profiles/r01_summary.md)
+  const bool pair = getenv("BQA_SMALL_PAIR") != nullptr;
   if (use_cluster)
     rc = launch_cluster(p, A, n_tasks);
+  else if (pair && threads == 1024)
+    rc = launch_small<512, 2>(p, A, n_tasks);
   else if (threads <= 128)
     rc = launch_small<128>(p, A, n_tasks);
   else if (threads <= 256)

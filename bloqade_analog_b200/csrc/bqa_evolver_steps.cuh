@@ -122,7 +122,7 @@ BQA_HD void TaskEvolver<Ctx>::step_dop853(int& accepted) {
     bool done = false;
     if constexpr (Ctx::kFastRhs) {
       if (!rot && ctx.exact_dim(P.dim)) {  // same sums in the same order, four elements per thread
-        ctx.final853_exact(h, atol, rtol, kk, yy, ynew, out, err, err3, stden);
+        ctx.final853_fast(P.dim, h, atol, rtol, kk, yy, ynew, out, err, err3, stden);
         done = true;
       }
     }

@@ -27,14 +27,16 @@ struct CtaCtxT {
   static constexpr int kLog = ilog2_ct(kT);
   double* red;  // shared scratch [3 * 32]
 
-  // ---- exact forms (dim == 4 * kT, two-level full space of kLog + 2 atoms) ----------------------------------
+  // ---- exact forms (dim == E * kT with E = 4 or 8 elements per thread, two-level full space) ----------------
   // Same arithmetic per element in the same order as the generic forms below => bit-identical results.  What
   // changes is the instruction count: ncu (profiles/r02_summary.md) showed 17 instructions per bit flip in the
   // generic loop (bounds branch, shift, index multiply, an unconditional subtract + two selects for the
-  // diagonal); here a flip is 1 LOP3 (shared by the thread's four elements) + LDS.128 + 2 DMUL + 2 DADD, and the
-  // diagonal subtract is predicated on the thread-index bit (warp-uniform for atoms >= 5) or known at compile time.
+  // diagonal); here a flip is 1 LOP3 (shared by four elements) + LDS.128 + 2 DMUL + 2 DADD, and the diagonal
+  // subtract is predicated on the thread-index bit (warp-uniform for atoms >= 5) or known at compile time.
+  // Element j of a thread is index tid + j * kT; they are processed in groups of four (register budget).
+  template <int E, int G>
   __device__ __forceinline__ void rhs_exact(const Coefs& C, const double* __restrict__ V, const cplx* ys, cplx* kout) {
-    constexpr int N = kLog + 2;
+    constexpr int N = kLog + (E == 16 ? 4 : E == 8 ? 3 : 2);
     const uint32_t tid = threadIdx.x;
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(ys);
     const uint32_t toff = tid * 16u;
@@ -43,114 +45,153 @@ struct CtaCtxT {
       asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(z.re), "=d"(z.im) : "r"(sbase + byte_off));
       return z;
     };
-    double ar[4] = {0.0, 0.0, 0.0, 0.0}, ai[4] = {0.0, 0.0, 0.0, 0.0}, dg[4];
+#pragma unroll 1
+    for (int g = 0; g < E; g += G) {
+      double ar[G], ai[G], dg[G];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) dg[j] = V ? __ldg(V + tid + (uint32_t)j * kT) : 0.0;
+      for (int j = 0; j < G; ++j) ar[j] = ai[j] = 0.0;
 #pragma unroll
-    for (int a = 0; a < N; ++a) {
-      const double cr = C.c_re[0][a], dl = C.delta[0][a];
-      if (a < kLog) {
-        if ((tid >> a) & 1u) {
+      for (int j = 0; j < G; ++j) dg[j] = V ? __ldg(V + tid + (uint32_t)(g + j) * kT) : 0.0;
 #pragma unroll
-          for (int j = 0; j < 4; ++j) dg[j] -= dl;
-        }
-        const uint32_t poff = toff ^ (16u << a);
+      for (int a = 0; a < N; ++a) {
+        const double cr = C.c_re[0][a], dl = C.delta[0][a];
+        if (a < kLog) {
+          if ((tid >> a) & 1u) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const cplx z = load(poff + (uint32_t)j * (kT * 16u));
-          ar[j] += cr * z.re;
-          ai[j] += cr * z.im;
-        }
-      } else {
-        const int jb = 1 << (a - kLog);
+            for (int j = 0; j < G; ++j) dg[j] -= dl;
+          }
+          const uint32_t poff = (toff ^ (16u << a)) + (uint32_t)g * (kT * 16u);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          if (j & jb) dg[j] -= dl;
-          const cplx z = load(toff + (uint32_t)(j ^ jb) * (kT * 16u));
-          ar[j] += cr * z.re;
-          ai[j] += cr * z.im;
+          for (int j = 0; j < G; ++j) {
+            const cplx z = load(poff + (uint32_t)j * (kT * 16u));
+            ar[j] += cr * z.re;
+            ai[j] += cr * z.im;
+          }
+        } else {
+          const int jb = 1 << (a - kLog);
+#pragma unroll
+          for (int j = 0; j < G; ++j) {
+            if ((g + j) & jb) dg[j] -= dl;
+            const cplx z = load(toff + (uint32_t)((g + j) ^ jb) * (kT * 16u));
+            ar[j] += cr * z.re;
+            ai[j] += cr * z.im;
+          }
         }
       }
-    }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const cplx zi = load(toff + (uint32_t)j * (kT * 16u));
-      kout[tid + (uint32_t)j * kT] = times_minus_i(cmake(dg[j] * zi.re + ar[j], dg[j] * zi.im + ai[j]));
+      for (int j = 0; j < G; ++j) {
+        const cplx zi = load(toff + (uint32_t)(g + j) * (kT * 16u));
+        kout[tid + (uint32_t)(g + j) * kT] = times_minus_i(cmake(dg[j] * zi.re + ar[j], dg[j] * zi.im + ai[j]));
+      }
     }
   }
 
+  template <int E, int G>
   __device__ __forceinline__ void stage_input_exact(double h, int nnz, const int* slot, const double* val,
                                                     cplx* const* kk, const cplx* yy, cplx* out) {
     const uint32_t tid = threadIdx.x;
-    double sr[4] = {0.0, 0.0, 0.0, 0.0}, si[4] = {0.0, 0.0, 0.0, 0.0};
-    for (int j = 0; j < nnz; ++j) {
-      const cplx* kp = kk[slot[j]] + tid;
-      const double v = val[j];
-      cplx kz[4];
+#pragma unroll 1
+    for (int g = 0; g < E; g += G) {
+      const uint32_t base = tid + (uint32_t)g * kT;
+      double sr[G], si[G];
 #pragma unroll
-      for (int e = 0; e < 4; ++e) kz[e] = kp[e * kT];
+      for (int e = 0; e < G; ++e) sr[e] = si[e] = 0.0;
+      for (int j = 0; j < nnz; ++j) {
+        const cplx* kp = kk[slot[j]] + base;
+        const double v = val[j];
+        cplx kz[G];
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        sr[e] += v * kz[e].re;
-        si[e] += v * kz[e].im;
+        for (int e = 0; e < G; ++e) kz[e] = kp[e * kT];
+#pragma unroll
+        for (int e = 0; e < G; ++e) {
+          sr[e] += v * kz[e].re;
+          si[e] += v * kz[e].im;
+        }
       }
-    }
-    const cplx* yp = yy + tid;
-    cplx* op = out + tid;
+      const cplx* yp = yy + base;
+      cplx* op = out + base;
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const cplx yz = yp[e * kT];
-      op[e * kT] = cmake(yz.re + h * sr[e], yz.im + h * si[e]);
+      for (int e = 0; e < G; ++e) {
+        const cplx yz = yp[e * kT];
+        op[e * kT] = cmake(yz.re + h * sr[e], yz.im + h * si[e]);
+      }
     }
   }
 
   // new solution + both error estimators + stiffness denominator of a DOP853 step (step_dop853's final pass,
-  // Schroedinger picture), four elements per thread with the term loops outermost.  The per-thread partial sums
+  // Schroedinger picture), four elements at a time with the term loops outermost.  The per-thread partial sums
   // err / err3 / stden accumulate element by element in the order of the generic loop (re before im).
+  template <int E, int G>
   __device__ __forceinline__ void final853_exact(double h, double atol, double rtol, cplx* const* kk, const cplx* yy,
                                                  cplx* ynew, cplx* ys_io, double& err, double& err3, double& stden) {
     const uint32_t tid = threadIdx.x;
-    double sr[4] = {0.0, 0.0, 0.0, 0.0}, si[4] = {0.0, 0.0, 0.0, 0.0};
-    double e5r[4] = {0.0, 0.0, 0.0, 0.0}, e5i[4] = {0.0, 0.0, 0.0, 0.0};
-    double e3r[4] = {0.0, 0.0, 0.0, 0.0}, e3i[4] = {0.0, 0.0, 0.0, 0.0};
-    auto accumulate = [&](int n, const int* slot, const double* val, double* accr, double* acci) {
-      for (int j = 0; j < n; ++j) {
-        const cplx* kp = kk[slot[j]] + tid;
-        const double v = val[j];
+#pragma unroll 1
+    for (int g = 0; g < E; g += G) {
+      const uint32_t base = tid + (uint32_t)g * kT;
+      double sr[G], si[G];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const cplx kz = kp[e * kT];
-          accr[e] += v * kz.re;
-          acci[e] += v * kz.im;
+      for (int e = 0; e < G; ++e) sr[e] = si[e] = 0.0;
+      double e5r[G], e5i[G], e3r[G], e3i[G];
+#pragma unroll
+      for (int e = 0; e < G; ++e) e5r[e] = e5i[e] = e3r[e] = e3i[e] = 0.0;
+      auto accumulate = [&](int n, const int* slot, const double* val, double* accr, double* acci) {
+        for (int j = 0; j < n; ++j) {
+          const cplx* kp = kk[slot[j]] + base;
+          const double v = val[j];
+#pragma unroll
+          for (int e = 0; e < G; ++e) {
+            const cplx kz = kp[e * kT];
+            accr[e] += v * kz.re;
+            acci[e] += v * kz.im;
+          }
         }
-      }
-    };
-    accumulate(tables::DOP853_b_nnz[0], tables::DOP853_b_slot[0], tables::DOP853_b_val[0], sr, si);
-    accumulate(tables::DOP853_e5_nnz[0], tables::DOP853_e5_slot[0], tables::DOP853_e5_val[0], e5r, e5i);
-    accumulate(tables::DOP853_e3_nnz[0], tables::DOP853_e3_slot[0], tables::DOP853_e3_val[0], e3r, e3i);
+      };
+      accumulate(tables::DOP853_b_nnz[0], tables::DOP853_b_slot[0], tables::DOP853_b_val[0], sr, si);
+      accumulate(tables::DOP853_e5_nnz[0], tables::DOP853_e5_slot[0], tables::DOP853_e5_val[0], e5r, e5i);
+      accumulate(tables::DOP853_e3_nnz[0], tables::DOP853_e3_slot[0], tables::DOP853_e3_val[0], e3r, e3i);
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const uint32_t i = tid + (uint32_t)e * kT;
-      const cplx yo = yy[i];
-      const cplx z = cmake(yo.re + h * sr[e], yo.im + h * si[e]);
-      double sk = atol + rtol * fmax(fabs(yo.re), fabs(z.re));
-      double q = e5r[e] / sk;
-      err += q * q;
-      q = e3r[e] / sk;
-      err3 += q * q;
-      sk = atol + rtol * fmax(fabs(yo.im), fabs(z.im));
-      q = e5i[e] / sk;
-      err += q * q;
-      q = e3i[e] / sk;
-      err3 += q * q;
-      ynew[i] = z;
-      const cplx old = ys_io[i];
-      const double dr = z.re - old.re, di = z.im - old.im;
-      stden += dr * dr + di * di;
-      ys_io[i] = z;
+      for (int e = 0; e < G; ++e) {
+        const uint32_t i = base + (uint32_t)e * kT;
+        const cplx yo = yy[i];
+        const cplx z = cmake(yo.re + h * sr[e], yo.im + h * si[e]);
+        double sk = atol + rtol * fmax(fabs(yo.re), fabs(z.re));
+        double q = e5r[e] / sk;
+        err += q * q;
+        q = e3r[e] / sk;
+        err3 += q * q;
+        sk = atol + rtol * fmax(fabs(yo.im), fabs(z.im));
+        q = e5i[e] / sk;
+        err += q * q;
+        q = e3i[e] / sk;
+        err3 += q * q;
+        ynew[i] = z;
+        const cplx old = ys_io[i];
+        const double dr = z.re - old.re, di = z.im - old.im;
+        stden += dr * dr + di * di;
+        ys_io[i] = z;
+      }
     }
   }
-  __device__ __forceinline__ bool exact_dim(int64_t dim) const { return kT > 0 && dim == 4 * (int64_t)kT; }
+  // elements per thread of the exact forms for this dim (0: use the generic forms); kG = elements handled together
+  // (more registers per thread => more independent loads in flight: 4 at 1024 threads / 64 registers, 8 below)
+  static constexpr int kG = 4;                       // flip loop and final pass
+  static constexpr int kGC = (kT >= 1024) ? 4 : 8;  // stage combine (pure streaming: loads in flight matter)
+  __device__ __forceinline__ int exact_elems(int64_t dim) const {
+    if (kT > 0 && dim == 4 * (int64_t)kT) return 4;
+    if (kT > 0 && dim == 8 * (int64_t)kT) return 8;
+    if (kT > 0 && dim == 16 * (int64_t)kT) return 16;
+    return 0;
+  }
+  __device__ __forceinline__ bool exact_dim(int64_t dim) const { return exact_elems(dim) != 0; }
+  __device__ __forceinline__ void final853_fast(int64_t dim, double h, double atol, double rtol, cplx* const* kk,
+                                                const cplx* yy, cplx* ynew, cplx* ys_io, double& err, double& err3,
+                                                double& stden) {
+    switch (exact_elems(dim)) {
+      case 4: final853_exact<4, 4>(h, atol, rtol, kk, yy, ynew, ys_io, err, err3, stden); break;
+      case 8: final853_exact<8, kG>(h, atol, rtol, kk, yy, ynew, ys_io, err, err3, stden); break;
+      default: final853_exact<16, kG>(h, atol, rtol, kk, yy, ynew, ys_io, err, err3, stden); break;
+    }
+  }
 
   // kout = -i H(t) ys for a two-level full space with real coefficients (TaskEvolver::fast_rhs).  Same
   // arithmetic in the same order as h_apply_element, so the result is bit-identical; what changes is the
@@ -211,9 +252,11 @@ struct CtaCtxT {
   // order as TaskEvolver::stage_input, so the result is bit-identical.
   __device__ __forceinline__ void stage_input_plain(int64_t dim64, double h, int nnz, const int* slot, const double* val,
                                                     cplx* const* kk, const cplx* yy, cplx* out) {
-    if (exact_dim(dim64)) {
-      stage_input_exact(h, nnz, slot, val, kk, yy, out);
-      return;
+    switch (exact_elems(dim64)) {
+      case 4: stage_input_exact<4, 4>(h, nnz, slot, val, kk, yy, out); return;
+      case 8: stage_input_exact<8, kGC>(h, nnz, slot, val, kk, yy, out); return;
+      case 16: stage_input_exact<16, kGC>(h, nnz, slot, val, kk, yy, out); return;
+      default: break;
     }
     const uint32_t dim = (uint32_t)dim64, bd = blockDim.x;
     for (uint32_t i0 = threadIdx.x; i0 < dim; i0 += 4u * bd) {
@@ -244,8 +287,12 @@ struct CtaCtxT {
 
   __device__ __forceinline__ void rhs_full2_real(int n, int64_t dim, const Coefs& C, const double* V, const cplx* ys,
                                                  cplx* kout) {
-    if (exact_dim(dim) && n == kLog + 2 && __isShared(ys))
-      rhs_exact(C, V, ys, kout);
+    if (exact_elems(dim) == 4 && n == kLog + 2 && __isShared(ys))
+      rhs_exact<4, 4>(C, V, ys, kout);
+    else if (exact_elems(dim) == 8 && n == kLog + 3 && __isShared(ys))
+      rhs_exact<8, kG>(C, V, ys, kout);
+    else if (exact_elems(dim) == 16 && n == kLog + 4 && __isShared(ys))
+      rhs_exact<16, kG>(C, V, ys, kout);
     else if (__isShared(ys))
       rhs_full2_real_impl<true>(n, (uint32_t)dim, C, V, ys, kout);
     else
@@ -340,8 +387,10 @@ struct SmallArgs {
   int vec_order[kNumVec];       // priority order: vec_order[r] = vector index with rank r
 };
 
-template <int kThreads>
-__global__ void __launch_bounds__(kThreads, 1) evolve_small_kernel(const SmallArgs A) {
+// kMinCtas = 2: two tasks share an SM (two CTAs of 512 threads at dim 4096): while one task streams K vectors
+// from L2 in its stage combine the other runs its shared-memory bound flip loop
+template <int kThreads, int kMinCtas = 1>
+__global__ void __launch_bounds__(kThreads, kMinCtas) evolve_small_kernel(const SmallArgs A) {
   extern __shared__ __align__(16) unsigned char dyn_smem[];
   __shared__ Coefs s_coefs;
   __shared__ Coefs s_tab[kCoefTab];           // coefficients of all stage times of the current step
