@@ -27,7 +27,7 @@ EXPORTS = [
     "bqa_plan_add_diagonal", "bqa_plan_build_rydberg", "bqa_plan_get_diagonal", "bqa_plan_add_csr",
     "bqa_apply", "bqa_evolve_batch", "bqa_run_batch", "bqa_norm", "bqa_normalize", "bqa_expectation",
     "bqa_local_trace", "bqa_sample", "bqa_plan_enable_timing", "bqa_plan_get_timing",
-    "bqa_shard_sync_bytes", "bqa_shard_alloc", "bqa_shard_open", "bqa_shard_close", "bqa_shard_free",
+    "bqa_shard_sync_bytes", "bqa_shard_alloc", "bqa_shard_open", "bqa_shard_close", "bqa_shard_free", "bqa_shard_reset",
     "bqa_plan_build_rydberg_shard", "bqa_apply_sharded", "bqa_evolve_sharded", "bqa_norm_noalloc", "bqa_current_device",
 ]
 
@@ -375,6 +375,11 @@ def shard_close(ptr: int):
 
 def shard_free(ptr: int):
     _check(load().bqa_shard_free(c_void_p(int(ptr))))
+
+
+def shard_reset(sync_ptr: int):
+    """zero this rank's barrier counters / abort word; a host barrier must follow before bqa_evolve_sharded"""
+    _check(load().bqa_shard_reset(c_void_p(int(sync_ptr))))
 
 
 def shard_sync_bytes() -> int:

@@ -82,6 +82,14 @@ int bqa_shard_free(void* dev_ptr) {
   return 0;
 }
 
+int bqa_shard_reset(void* sync_own) {
+  BQA_ENTER();
+  if (!sync_own) return fail("bqa_shard_reset: null argument");
+  CK(cudaMemset(sync_own, 0, (size_t)kShardFlagBytes));  // barrier counter, barrier count, abort word
+  CK(cudaDeviceSynchronize());
+  return 0;
+}
+
 int bqa_plan_build_rydberg_shard(bqa_plan* p, int32_t n_total, const double* pair_host, int32_t rank, int32_t* diag_id) {
   BQA_ENTER_PLAN(p);
   if (!p || !pair_host || !diag_id) return fail("bqa_plan_build_rydberg_shard: null argument");

@@ -51,6 +51,7 @@ enum : int {
   kStatusNeedSteps = -2,
   kStatusStepTooSmall = -3,
   kStatusStiff = -4,
+  kStatusPeerAbort = -6,  // sharded state only (no scipy counterpart): a peer rank failed / a cross-rank barrier timed out
 };
 
 enum : int { kSolverDopri5 = 5, kSolverDop853 = 8 };

@@ -27,6 +27,8 @@ struct LargeCtrl {
   // take identical decisions.  peer_partial[r] / peer_flag[r] are rank r's partial-sum array and barrier
   // counter, mapped into this process (CUDA IPC, NVLink peer access); world <= 1: not sharded.
   int world, rank;
+  int aborted;                           // a barrier saw the abort word or timed out (lg_mark_abort)
+  unsigned long long barrier_timeout_ns; // bound of one barrier's spin
   double* peer_partial[8];
   unsigned long long* peer_flag[8];
 };
@@ -154,28 +156,80 @@ __device__ __forceinline__ void lg_total3(const LargeCtrl* ctl, double& a, doubl
   }
 }
 
+// Sync block of a rank (bqa_api_shard.cuh), first 64 bytes: u64 [0] barrier counter (every rank adds to it),
+// [1] barrier count of this rank (only its owner touches it), [2] abort word (any rank may set it).
+enum : int { kFlagCounter = 0, kFlagEpoch = 1, kFlagAbort = 2 };
+
+__device__ __forceinline__ unsigned long long lg_globaltimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// a peer failed or a barrier timed out: this rank's evolution ends with kStatusPeerAbort, every kernel of the
+// launch list that follows returns at once (active = 0) and the host's next poll sees `done`
+__device__ __forceinline__ void lg_mark_abort(LargeCtrl* ctl) {
+  ctl->aborted = 1;
+  ctl->active = 0;
+  ctl->accepted = 0;
+  if (ctl->c.status >= 0) ctl->c.status = kStatusPeerAbort;
+  ctl->c.done = 1;
+}
+
 // Cross-rank barrier of a sharded run, device initiated: every rank adds 1 to every rank's counter over
 // NVLink, then spins on its own counter.  Writes of the kernels before it (stage input ys, partial sums) are
-// published by the system-scope fence; launched <<<1, 32>>> on the engine's stream.
+// published by the system-scope fence; launched <<<1, 32>>> on the engine's stream.  The spin is BOUNDED
+// (LargeCtrl::barrier_timeout_ns) and polls the abort word of this rank's sync block: a rank that fails on the
+// host (lg_abort_peers) or times out sets the abort word of EVERY rank, so one failed rank ends the others with
+// kStatusPeerAbort instead of hanging them.  Counters are reset by bqa_shard_reset before each evolve call.
 __global__ void lg_barrier(LargeCtrl* ctl) {
   const int world = ctl->world;
   if (world <= 1) return;
   __shared__ unsigned long long target;
+  __shared__ int dead;
+  unsigned long long* own = ctl->peer_flag[ctl->rank];
   if (threadIdx.x == 0) {
-    // the barrier count lives next to the counter (slot 1, only this rank touches it), so it carries over
-    // from one evolve call to the next without a reset
-    unsigned long long* epoch = ctl->peer_flag[ctl->rank] + 1;
-    *epoch += 1;
-    target = *epoch * (unsigned long long)world;
+    dead = (ctl->aborted || *(volatile unsigned long long*)(own + kFlagAbort) != 0ull) ? 1 : 0;
+    if (!dead) {
+      unsigned long long* epoch = own + kFlagEpoch;
+      *epoch += 1;
+      target = *epoch * (unsigned long long)world;
+    }
   }
   __syncthreads();
+  if (dead) {
+    if (threadIdx.x == 0) lg_mark_abort(ctl);
+    return;
+  }
   __threadfence_system();
-  if ((int)threadIdx.x < world) atomicAdd_system(ctl->peer_flag[threadIdx.x], 1ull);
+  if ((int)threadIdx.x < world) atomicAdd_system(ctl->peer_flag[threadIdx.x] + kFlagCounter, 1ull);
   if (threadIdx.x == 0) {
-    const volatile unsigned long long* mine = ctl->peer_flag[ctl->rank];
-    while (*mine < target) __nanosleep(200);
+    const volatile unsigned long long* mine = own + kFlagCounter;
+    const volatile unsigned long long* abort_word = own + kFlagAbort;
+    const unsigned long long t0 = lg_globaltimer();
+    unsigned int polls = 0;
+    while (*mine < target) {
+      __nanosleep(200);
+      if ((++polls & 63u) == 0u && (*abort_word != 0ull || lg_globaltimer() - t0 > ctl->barrier_timeout_ns)) {
+        dead = 1;
+        break;
+      }
+    }
   }
   __syncthreads();
+  if (dead) {
+    if ((int)threadIdx.x < world) atomicExch_system(ctl->peer_flag[threadIdx.x] + kFlagAbort, 1ull);
+    if (threadIdx.x == 0) lg_mark_abort(ctl);
+  }
+  __threadfence_system();
+}
+
+// host-side failure of a rank inside a sharded evolve: tell every rank (this one included)
+struct LgPeerFlags {
+  unsigned long long* f[8];
+};
+__global__ void lg_abort_peers(const LgPeerFlags F, int world) {
+  if ((int)threadIdx.x < world && F.f[threadIdx.x]) atomicExch_system(F.f[threadIdx.x] + kFlagAbort, 1ull);
   __threadfence_system();
 }
 

@@ -92,10 +92,32 @@ struct LgShard {
   unsigned long long* peer_flag[8];
 };
 
-static int evolve_large_device(bqa_plan* p, const double* d_records, const std::vector<int64_t>& h_off,
-                               const double* h_records, int n_tasks, const bqa_solver_opts* o, const cplx* d_psi0,
-                               int psi0_mode, const double* h_times, int n_times, cplx* d_out, TaskStats* d_stats,
-                               const LgShard* sh = nullptr) {
+// scratch of one streamed-engine call, released on every exit path
+struct LgScratch {
+  cplx* work = nullptr;
+  LargeCtrl* ctl = nullptr;
+  double* partial = nullptr;
+  bool own_partial = false;
+  int* h_done = nullptr;
+  ~LgScratch() {
+    cudaFree(work);
+    cudaFree(ctl);
+    if (own_partial) cudaFree(partial);
+    if (h_done) cudaFreeHost(h_done);
+  }
+};
+
+// bound of one cross-rank barrier spin (BQA_BARRIER_TIMEOUT_MS, default 60 s)
+static unsigned long long lg_barrier_timeout_ns() {
+  const char* e = getenv("BQA_BARRIER_TIMEOUT_MS");
+  const double ms = e ? atof(e) : 60000.0;
+  return (unsigned long long)(std::max(1.0, ms) * 1e6);
+}
+
+static int evolve_large_run(bqa_plan* p, LgScratch& X, const double* d_records, const std::vector<int64_t>& h_off,
+                            const double* h_records, int n_tasks, const bqa_solver_opts* o, const cplx* d_psi0,
+                            int psi0_mode, const double* h_times, int n_times, cplx* d_out, TaskStats* d_stats,
+                            const LgShard* sh) {
   const int64_t dim = p->P.dim;
   const int world = sh ? sh->world : 1;
   const int64_t dim_total = dim * world;
@@ -105,10 +127,6 @@ static int evolve_large_device(bqa_plan* p, const double* d_records, const std::
   // reduction-style kernels: a multiple of the SM count, capped by the amount of work
   const int gs = (int)std::max<int64_t>(1, std::min<int64_t>((dim + kLgThreads - 1) / kLgThreads, (int64_t)p->sm_count * 4));
   const int ga = grid_for(p, dim, kApplyThreads);
-  cplx* work = nullptr;
-  LargeCtrl* ctl = nullptr;
-  double* partial = nullptr;
-  int* h_done = nullptr;
   // RHS form: shared-memory-tiled passes when the operator allows it (always for a sharded state)
   LgRhsPlan R;
   R.world = world;
@@ -127,13 +145,18 @@ static int evolve_large_device(bqa_plan* p, const double* d_records, const std::
       once_per_device(attr_set, true);
     }
   }
-  CK(cudaMalloc(&work, sizeof(cplx) * dim * n_vec));
-  CK(cudaMalloc(&ctl, sizeof(LargeCtrl)));
-  if (sh)
-    partial = sh->partial;
-  else
-    CK(cudaMalloc(&partial, sizeof(double) * 4 * gs));
-  CK(cudaMallocHost(&h_done, 2 * sizeof(int)));
+  CK(cudaMalloc(&X.work, sizeof(cplx) * dim * n_vec));
+  CK(cudaMalloc(&X.ctl, sizeof(LargeCtrl)));
+  if (sh) {
+    X.partial = sh->partial;
+  } else {
+    CK(cudaMalloc(&X.partial, sizeof(double) * 4 * gs));
+    X.own_partial = true;
+  }
+  CK(cudaMallocHost(&X.h_done, 2 * sizeof(int)));
+  cplx* work = X.work;
+  LargeCtrl* ctl = X.ctl;
+  int* h_done = X.h_done;
   int rc = 0;
   const int steps_per_poll = dim >= (1 << 22) ? 4 : (dim >= (1 << 16) ? 16 : 64);
   for (int task = 0; task < n_tasks && !rc; ++task) {
@@ -150,12 +173,13 @@ static int evolve_large_device(bqa_plan* p, const double* d_records, const std::
       hc.vec[kVecYs] = sh->ys;
       hc.world = sh->world;
       hc.rank = sh->rank;
+      hc.barrier_timeout_ns = lg_barrier_timeout_ns();
       for (int r = 0; r < sh->world; ++r) {
         hc.peer_partial[r] = sh->peer_partial[r];
         hc.peer_flag[r] = sh->peer_flag[r];
       }
     }
-    hc.partial = partial;
+    hc.partial = X.partial;
     hc.n_blocks = gs;
     hc.active = 1;
     if (cudaMemcpyAsync(ctl, &hc, sizeof(hc), cudaMemcpyHostToDevice, s) != cudaSuccess) { rc = fail("ctl upload failed"); break; }
@@ -199,15 +223,29 @@ static int evolve_large_device(bqa_plan* p, const double* d_records, const std::
         t_cur = t_next;
       }
       lg_emit<<<gs, kLgThreads, 0, s>>>(ctl, dim, V, t_cur, d_out ? d_out + ((int64_t)task * n_times + k) * dim : nullptr,
-                                        d_stats ? d_stats + (int64_t)task * n_times + k : nullptr, ran);
+                                        d_stats ? d_stats + (int64_t)task * n_times + k : nullptr, ran, failed ? 1 : 0);
       LAUNCHED();
     }
     cudaError_t e = cudaStreamSynchronize(s);
     if (!rc && e != cudaSuccess) rc = fail("streamed engine: %s", cudaGetErrorString(e));
   }
-  cudaFree(work);
-  cudaFree(ctl);
-  if (!sh) cudaFree(partial);
-  cudaFreeHost(h_done);
+  return rc;
+}
+
+static int evolve_large_device(bqa_plan* p, const double* d_records, const std::vector<int64_t>& h_off,
+                               const double* h_records, int n_tasks, const bqa_solver_opts* o, const cplx* d_psi0,
+                               int psi0_mode, const double* h_times, int n_times, cplx* d_out, TaskStats* d_stats,
+                               const LgShard* sh = nullptr) {
+  LgScratch X;
+  const int rc = evolve_large_run(p, X, d_records, h_off, h_records, n_tasks, o, d_psi0, psi0_mode, h_times, n_times, d_out,
+                                  d_stats, sh);
+  if (rc && sh) {
+    // this rank failed on the host (allocation, launch, ...): release the peers from their barriers.  The error
+    // text of the failure itself stays in bqa_last_error.
+    LgPeerFlags F;
+    for (int r = 0; r < 8; ++r) F.f[r] = r < sh->world ? sh->peer_flag[r] : nullptr;
+    lg_abort_peers<<<1, 32, 0, p->stream>>>(F, sh->world);
+    cudaStreamSynchronize(p->stream);
+  }
   return rc;
 }

@@ -186,9 +186,10 @@ __global__ void lg_ctl_end853(LargeCtrl* ctl) {
   c.step_end(ctl->o, ctl->accepted);
 }
 
-// out = (u(t)*) y, stats
+// out = (u(t)*) y, stats.  ran = 0: no integration for this output time (t equals the previous one, or an earlier
+// output time of the task failed - then the entry is marked kStatusInconsistent like evolve_small_kernel does)
 __global__ void __launch_bounds__(kLgThreads)
-lg_emit(LargeCtrl* ctl, int64_t dim, const double* __restrict__ V, double t, cplx* out, TaskStats* st, int ran) {
+lg_emit(LargeCtrl* ctl, int64_t dim, const double* __restrict__ V, double t, cplx* out, TaskStats* st, int ran, int failed) {
   const bool rot = ctl->o.interaction != 0 && V != nullptr;
   const cplx* y = ctl->vec[kVecY];
   if (out) {
@@ -209,7 +210,7 @@ lg_emit(LargeCtrl* ctl, int64_t dim, const double* __restrict__ V, double t, cpl
       s.h_last = ctl->c.h;
       s.t_last = ctl->c.x;
     } else {
-      s.status = kStatusOk;
+      s.status = failed ? kStatusInconsistent : kStatusOk;
       s.nfcn = s.nstep = s.naccpt = s.nrejct = 0;
       s.h_last = 0.0;
       s.t_last = t;

@@ -128,6 +128,7 @@ class ShardedHamiltonian:
         opts = _lib.make_opts(solver_name, atol, rtol, nsteps, False, reject_mode, "streamed")
         out = torch.empty((times.size, self.local_dim), dtype=torch.complex128, device=f"cuda:{self.device}")
         p0 = None if psi0_local is None else int(psi0_local.contiguous().data_ptr())
+        _lib.shard_reset(self._sync)  # barrier counters / abort word back to zero, ranks in step again
         dist.barrier(group=self.group)
         stats = self.plan.evolve_sharded(self.record, opts, self.desc, times, out.data_ptr(), p0)
         dist.barrier(group=self.group)

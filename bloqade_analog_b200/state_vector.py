@@ -226,6 +226,7 @@ _DOP_ERRORS = {
     -2: "DOP853/DOPRI5: Larger nsteps is needed.",
     -3: "DOP853/DOPRI5: Step size becomes too small.",
     -4: "DOP853/DOPRI5: Problem is probably stiff (interrupted).",
+    -6: "sharded state: a peer rank failed or a cross-rank barrier timed out.",
 }
 
 

@@ -40,6 +40,7 @@ extern "C" {
 #define BQA_STATUS_NEED_STEPS (-2)
 #define BQA_STATUS_STEP_TOO_SMALL (-3)
 #define BQA_STATUS_STIFF (-4)
+#define BQA_STATUS_PEER_ABORT (-6) /* sharded state only: a peer rank failed or a cross-rank barrier timed out */
 
 #define BQA_ENGINE_AUTO 0
 #define BQA_ENGINE_CTA_PER_TASK 1 /* kernel (5): whole integration inside one CTA per task        */
@@ -216,6 +217,12 @@ int bqa_shard_alloc(int64_t bytes, void** dev_ptr, void* handle64);
 int bqa_shard_open(const void* handle64, void** peer_ptr);
 int bqa_shard_close(void* peer_ptr);
 int bqa_shard_free(void* dev_ptr);
+/* Zero the barrier counters and the abort word of THIS rank's sync block.  Every rank calls it, then a host-side
+ * barrier (torch.distributed / MPI), before each bqa_evolve_sharded: the cross-rank barriers of the integrator
+ * are device initiated with a bounded spin (BQA_BARRIER_TIMEOUT_MS, default 60000) and an abort word, so a rank
+ * that fails or stalls ends the others with status BQA_STATUS_PEER_ABORT (-6) instead of hanging them, and the
+ * reset brings the ranks back in step afterwards.  No reference counterpart (single-process NumPy state). */
+int bqa_shard_reset(void* sync_own);
 /* van-der-Waals diagonal of this rank's shard, same pair order as hamiltonian.py:76-89; pair_host is
  * [n_atoms_total][n_atoms_total] */
 int bqa_plan_build_rydberg_shard(bqa_plan* plan, int32_t n_atoms_total, const double* pair_host, int32_t rank,

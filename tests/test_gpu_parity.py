@@ -330,6 +330,19 @@ def test_failed_task_does_not_poison_batch():
         run_programs(progs, 10, nsteps=2000)
 
 
+@pytest.mark.parametrize("engine", ["cta", "cluster", "streamed"])
+def test_output_times_after_a_failure_are_marked(engine):
+    """three output times, nsteps (400) too small for the second: the first entry succeeds, the second carries the
+    integrator's status (-2) and every later one is -1 (not "success" with a stale state) on every engine"""
+    h = ham("c1_square3_a5")
+    d = h.emulator_ir.duration
+    opts = _lib.make_opts("dop853", 1e-7, 1e-14, 400, False, 1, engine)
+    blob, offsets = lowering.concat_records([h.record])
+    _, stats = h.plan.evolve_batch(blob, offsets, np.array([[0.02 * d, 0.7 * d, d]]), opts)
+    st = np.asarray(stats).reshape(-1)
+    assert [int(x) for x in st["status"]] == [1, -2, -1], st["status"]
+
+
 def test_gate_run_seeded_matches_reference_shots():
     c, h = golden_case("c1_square3_a6p5_short"), ham("c1_square3_a6p5_short")
     import zlib
@@ -475,6 +488,46 @@ def test_sharded_apply_equals_unsharded(world, n_atoms):
                 assert np.array_equal(plan.get_diagonal(did), h.plan.get_diagonal(h.diag_id)[rank * ldim:(rank + 1) * ldim])
             plan.close()
     h.plan.close()
+
+
+def test_sharded_barrier_is_bounded_when_a_peer_never_arrives(monkeypatch):
+    """rank 0 of a 2-rank sharded evolve whose peer never shows up (its buffers are plain allocations of this
+    process): the device-initiated barrier gives up after BQA_BARRIER_TIMEOUT_MS, sets the abort word of every rank
+    and the call returns status -6 instead of hanging; after bqa_shard_reset the sync block is clean again"""
+    import time
+    import torch
+
+    monkeypatch.setenv("BQA_BARRIER_TIMEOUT_MS", "300")
+    n_atoms, ldim = 15, 1 << 14
+    from bloqade_analog_b200.lowering import pack_task_record, pair_interactions
+
+    prog = programs.adiabatic_program(ir.chain_sites(n_atoms, lattice_spacing=5.5), durations=[0.01, 0.02, 0.01])
+    plan = _lib.Plan(n_atoms - 1, 2, ldim)
+    did = plan.build_rydberg_shard(pair_interactions(prog.register), 0)
+    rec = pack_task_record(prog, did)
+    bufs = [_lib.shard_alloc(16 * ldim)[0] for _ in range(2)]
+    syncs = [_lib.shard_alloc(_lib.shard_sync_bytes())[0] for _ in range(2)]
+    desc = _lib.ShardDesc(2, 0, n_atoms, 0)
+    for r in range(2):
+        desc.ys[r], desc.sync[r] = bufs[r], syncs[r]
+    out = torch.empty((1, ldim), dtype=torch.complex128, device="cuda")
+    opts = _lib.make_opts("dop853", 1e-7, 1e-14, engine="streamed")
+    t0 = time.perf_counter()
+    stats = plan.evolve_sharded(rec, opts, desc, np.array([prog.duration]), out.data_ptr(), None)
+    assert time.perf_counter() - t0 < 30.0
+    assert int(stats["status"][0]) == -6
+
+    def flags(ptr):
+        class H:
+            __cuda_array_interface__ = {"shape": (8,), "typestr": "<u8", "data": (ptr, False), "version": 2, "strides": None}
+        return torch.as_tensor(H(), device="cuda").cpu().numpy().copy()
+
+    assert flags(syncs[0])[2] == 1 and flags(syncs[1])[2] == 1  # abort word set on both ranks
+    _lib.shard_reset(syncs[0])
+    assert not flags(syncs[0]).any()
+    for b in bufs + syncs:
+        _lib.shard_free(b)
+    plan.close()
 
 
 def test_streamed_engine_tiled_rhs_equals_gather_rhs(monkeypatch):
