@@ -4,6 +4,7 @@
 #include <stdlib.h>
 
 #include "bqa_cluster_launch.h"
+#include "bqa_small_launch.h"
 #include "bqa_large.cuh"
 #include "bqa_large_host.cuh"
 
@@ -11,14 +12,17 @@
 // are re-read by the most stage combines, then y.
 static const int kOrder853[kNumVec] = {kVecYs, kVecK + 0, kVecK + 3, kVecK + 4, kVecY, kVecK + 5,
                                        kVecK + 6, kVecK + 7, kVecK + 8, kVecK + 9, kVecK + 1, kVecK + 2};
+// fused DOP853 step of the CTA engine (CtaCtxT::step853_fused): y instead of k4 - with the just-computed K
+// carried in registers, y (read by every stage) is the vector whose L2 reads are worth most
+static const int kOrder853Fused[kNumVec] = {kVecYs, kVecK + 0, kVecY, kVecK + 3, kVecK + 4, kVecK + 5,
+                                            kVecK + 6, kVecK + 7, kVecK + 8, kVecK + 9, kVecK + 1, kVecK + 2};
 static const int kOrder5[kNumVec] = {kVecYs, kVecK + 0, kVecK + 1, kVecY, kVecK + 6, kVecK + 2,
                                      kVecK + 3, kVecK + 4, kVecK + 5, kVecK + 7, kVecK + 8, kVecK + 9};
 
 template <int kThreads, int kMinCtas = 1>
 static int launch_small(bqa_plan* p, SmallArgs& A, int n_tasks) {
-  auto kern = evolve_small_kernel<kThreads, kMinCtas>;
   cudaFuncAttributes fa;
-  CK(cudaFuncGetAttributes(&fa, kern));
+  CK((small_kernel_attributes<kThreads, kMinCtas>(&fa)));
   const int64_t vec_bytes = (int64_t)sizeof(cplx) * A.P.dim;
   const int64_t dyn_max = p->smem_optin - (int64_t)fa.sharedSizeBytes - 1024;
   int n_smem = (int)std::min<int64_t>(A.n_vec, dyn_max / vec_bytes);
@@ -27,12 +31,16 @@ static int launch_small(bqa_plan* p, SmallArgs& A, int n_tasks) {
   if (n_smem < 0) n_smem = 0;
   // tiny states: leave room for several CTAs per SM instead of hoarding shared memory
   size_t dyn = (size_t)n_smem * vec_bytes;
-  CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(dyn, 1024)));
   int occ = 1;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, dyn));
+  CK((small_kernel_occupancy<kThreads, kMinCtas>(dyn, &occ)));
   if (occ < 1) return fail("evolve kernel does not fit on an SM (threads=%d, smem=%zu)", kThreads, dyn);
   const int grid = (int)std::min<int64_t>(n_tasks, (int64_t)occ * p->sm_count);
   A.n_smem_vecs = n_smem;
+  A.fused_layout = (A.fused_layout && n_smem >= 3 && kMinCtas == 1) ? 1 : 0;
+  // tensor memory as storage of four K vectors: one CTA per SM (a second one could not allocate its columns),
+  // 16 * dim / threads columns per thread <= 512 * 128 / threads, i.e. dim <= 4096
+  A.use_tmem = (A.fused_layout && occ == 1 && A.P.dim <= 4096 && A.P.dim % kThreads == 0 &&
+                getenv("BQA_NO_TMEM") == nullptr) ? 1 : 0;
   A.gws_stride = (int64_t)(A.n_vec - n_smem) * A.P.dim;
   cplx* gws = nullptr;
   if (A.gws_stride > 0) {
@@ -40,9 +48,8 @@ static int launch_small(bqa_plan* p, SmallArgs& A, int n_tasks) {
   }
   A.gws = gws;
   if (p->timing) cudaEventRecord(p->ev0, p->stream);
-  kern<<<grid, kThreads, dyn, p->stream>>>(A);
+  cudaError_t e = small_kernel_launch<kThreads, kMinCtas>(A, grid, dyn, p->stream);
   LAUNCHED();
-  cudaError_t e = cudaGetLastError();
   if (p->timing) cudaEventRecord(p->ev1, p->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
   if (p->timing && e == cudaSuccess) {
@@ -151,7 +158,12 @@ static int evolve_small_device(bqa_plan* p, const double* d_records, const int64
   A.o.reject_mode = o->reject_mode;
   const bool d5 = o->solver == BQA_SOLVER_DOPRI5;
   A.n_vec = d5 ? 9 : 12;
-  memcpy(A.vec_order, d5 ? kOrder5 : kOrder853, sizeof(A.vec_order));
+  // the fused step needs: dop853, two-level full space, no CSR term, Schroedinger picture (the device also checks
+  // that the task has no phase waveform and that dim = 4 or 8 elements per thread)
+  const bool fused = !d5 && !use_cluster && p->P.full_space && p->P.n_level == 2 && p->P.n_csr == 0 &&
+                     !o->interaction_picture && getenv("BQA_NO_FUSED_STEP") == nullptr;
+  A.fused_layout = fused ? 1 : 0;
+  memcpy(A.vec_order, d5 ? kOrder5 : (fused ? kOrder853Fused : kOrder853), sizeof(A.vec_order));
   // work queue: longest final time first
   std::vector<int32_t> order(n_tasks);
   std::iota(order.begin(), order.end(), 0);

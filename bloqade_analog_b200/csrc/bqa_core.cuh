@@ -491,7 +491,8 @@ struct Controller {
   double hnew, fac11;
   BQA_HD int decide(const SolverOpts& o, double err) {
     fac11 = pow(err, expo1);
-    double fac = fac11 / pow(facold, o.beta);
+    // beta = 0 (SciPy's setting for dop853): pow(facold, 0) is exactly 1 and x / 1 is x - skip the call
+    double fac = (o.beta == 0.0) ? fac11 : fac11 / pow(facold, o.beta);
     fac = fmax(facc2, fmin(facc1, fac / o.safety));
     hnew = h / fac;
     if (err <= 1.0) {
@@ -501,7 +502,8 @@ struct Controller {
     }
     return 0;
   }
-  BQA_HD bool stiff_due(const SolverOpts& o) const { return (naccpt % o.nstiff == 0) || iasti > 0; }
+  // 32-bit operands: naccpt <= nmax < 2^31, and a 64-bit remainder is a ~100-instruction software routine per thread
+  BQA_HD bool stiff_due(const SolverOpts& o) const { return ((uint32_t)naccpt % (uint32_t)o.nstiff == 0u) || iasti > 0; }
   // stiffness test after an accepted step (sums are over all real components)
   BQA_HD void stiff_update(const SolverOpts& o, double stnum, double stden) {
     if (stden > 0.0) hlamb = ((o.solver == kSolverDopri5) ? h : fabs(h)) * sqrt(stnum / stden);

@@ -40,6 +40,8 @@ struct Workspace {
   // every stage - ncu showed the whole CTA waiting at the stage barrier for the one warp that evaluates the
   // waveforms (19 % of the stall samples of evolve_small_kernel).  nullptr: evaluate per stage.
   Coefs* coefs_tab = nullptr;
+  // y, ys and K slot 0 sit in on-chip memory under pointers that must not be swapped (CtaCtxT::step853_fused)
+  bool fused_layout = false;
 };
 
 template <class Ctx>

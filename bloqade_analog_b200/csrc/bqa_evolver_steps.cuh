@@ -90,6 +90,10 @@ BQA_HD void TaskEvolver<Ctx>::step_dopri5(int& accepted) {
 // ---- DOP853: 12 stages; K slots 0..9, k11 -> slot 1, k12 -> slot 2, ynew -> slot 4 (k5 is dead)
 template <class Ctx>
 BQA_HD void TaskEvolver<Ctx>::step_dop853(int& accepted) {
+  if constexpr (Ctx::kFastRhs) {
+    // CTA engine, two-level full space with real coefficients: register-carry form of the same step
+    if (fast_rhs && w.fused_layout && ctx.step853_fused(*this, accepted)) return;
+  }
   const double x = c.x, h = c.h, tn = x + h;
   const int64_t n_real = 2 * P.dim;
   auto stage_time = [=](int s) { return (s == 10) ? tn : x + tables::DOP853_c[s + 1] * h; };

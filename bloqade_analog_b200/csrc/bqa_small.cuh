@@ -16,7 +16,61 @@
 
 namespace bqa {
 
-constexpr int ilog2_ct(int v) { return v <= 1 ? 0 : 1 + ilog2_ct(v / 2); }
+__host__ __device__ constexpr int ilog2_ct(int v) { return v <= 1 ? 0 : 1 + ilog2_ct(v / 2); }
+
+// ---- tensor memory (TMEM, 256 KB per SM) as thread-private vector storage ------------------------------------
+// The K vectors of the integrator are only ever touched element-wise by the thread that owns the element (the
+// bit-flip gathers read ys alone), so they do not need shared memory: four of them live in TMEM, which no other
+// unit of this kernel uses (no tcgen05.mma here).  A warp reaches the 32 TMEM lanes of its quarter (warp % 4) with
+// tcgen05.ld / tcgen05.st.32x32b: thread = lane, and the thread's elements lie along the columns.
+constexpr uint32_t kTmemCols = 512;
+__device__ __forceinline__ void tmem_alloc_all(uint32_t* smem_slot) {  // one warp
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(smem_slot);
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(a), "n"(kTmemCols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_free_all(uint32_t taddr) {  // one warp
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kTmemCols) : "memory");
+}
+// four complex numbers (16 columns) of this thread
+__device__ __forceinline__ void tmem_st4(uint32_t taddr, const cplx* z) {
+  uint32_t r[16];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    r[4 * e + 0] = (uint32_t)__double2loint(z[e].re);
+    r[4 * e + 1] = (uint32_t)__double2hiint(z[e].re);
+    r[4 * e + 2] = (uint32_t)__double2loint(z[e].im);
+    r[4 * e + 3] = (uint32_t)__double2hiint(z[e].im);
+  }
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+      "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+// load + wait; the registers pass through the wait statement so that no use of them can be scheduled before it
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, cplx* z) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
+                 "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+               :
+               : "memory");
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    z[e].re = __hiloint2double((int)r[4 * e + 1], (int)r[4 * e + 0]);
+    z[e].im = __hiloint2double((int)r[4 * e + 3], (int)r[4 * e + 2]);
+  }
+}
+// K slots 3..6 (k4..k7: the slots the stage combines re-read most after k1) are the TMEM residents
+__device__ __forceinline__ int tmem_index_of_slot(int slot) { return (slot >= 3 && slot <= 6) ? slot - 3 : -1; }
 
 // kT: the CTA size when it is known at compile time (0: not known).  With dim == 4 * kT every thread owns exactly
 // the four elements tid + j * kT and the hot loops below have "exact" forms without bounds checks, with the
@@ -26,6 +80,14 @@ struct CtaCtxT {
   static constexpr bool kFastRhs = true;
   static constexpr int kLog = ilog2_ct(kT);
   double* red;  // shared scratch [3 * 32]
+  // TMEM address of this thread's first column (vector 0, element 0); kNoTmem: K vectors stay in the L2 workspace
+  static constexpr uint32_t kNoTmem = 0xffffffffu;
+  uint32_t tm_base = kNoTmem;
+  // columns of one vector per thread: E elements x 4 (re/im x two 32-bit halves)
+  template <int E>
+  __device__ __forceinline__ uint32_t tm_addr(int tm_vec, int elem) const {
+    return tm_base + (uint32_t)(tm_vec * (4 * E) + 4 * elem);
+  }
 
   // ---- exact forms (dim == E * kT with E = 4 or 8 elements per thread, two-level full space) ----------------
   // Same arithmetic per element in the same order as the generic forms below => bit-identical results.  What
@@ -191,6 +253,271 @@ struct CtaCtxT {
       case 8: final853_exact<8, kG>(h, atol, rtol, kk, yy, ynew, ys_io, err, err3, stden); break;
       default: final853_exact<16, kG>(h, atol, rtol, kk, yy, ynew, ys_io, err, err3, stden); break;
     }
+  }
+
+  // ---- fused DOP853 step (step853_fused below): the K values a thread has just computed for its own E elements
+  // stay in registers (`kc`) for the stage combine / final pass that follows - that term is always the LAST one
+  // of the next Butcher row - so each stage reads one vector less from L2; flips of the top log2(E) atoms are
+  // register moves between the thread's own elements (ys is read once per element for them instead of once per
+  // flip).  Per element the arithmetic and its order are those of rhs_exact / stage_input_exact /
+  // final853_exact, so the results are bit-identical.
+  template <int E>
+  __device__ __forceinline__ void rhs_carry(const Coefs& C, const double* __restrict__ V, const cplx* ys, cplx* kout,
+                                            cplx (&kc)[E], bool store, int tm_vec = -1) {
+    constexpr int kLogE = ilog2_ct(E);
+    constexpr int N = kLog + kLogE;
+    constexpr int G = 4;
+    const uint32_t tid = threadIdx.x;
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(ys);
+    const uint32_t toff = tid * 16u;
+    auto load = [&](uint32_t byte_off) -> cplx {
+      cplx z;
+      asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(z.re), "=d"(z.im) : "r"(sbase + byte_off));
+      return z;
+    };
+    cplx zi[E];
+#pragma unroll
+    for (int j = 0; j < E; ++j) zi[j] = load(toff + (uint32_t)j * (kT * 16u));
+#pragma unroll
+    for (int g = 0; g < E; g += G) {
+      double ar[G], ai[G], dg[G];
+#pragma unroll
+      for (int j = 0; j < G; ++j) ar[j] = ai[j] = 0.0;
+#pragma unroll
+      for (int j = 0; j < G; ++j) dg[j] = V ? __ldg(V + tid + (uint32_t)(g + j) * kT) : 0.0;
+#pragma unroll
+      for (int a = 0; a < N; ++a) {
+        const double cr = C.c_re[0][a], dl = C.delta[0][a];
+        if (a < kLog) {
+          if ((tid >> a) & 1u) {
+#pragma unroll
+            for (int j = 0; j < G; ++j) dg[j] -= dl;
+          }
+          const uint32_t poff = (toff ^ (16u << a)) + (uint32_t)g * (kT * 16u);
+#pragma unroll
+          for (int j = 0; j < G; ++j) {
+            const cplx z = load(poff + (uint32_t)j * (kT * 16u));
+            ar[j] += cr * z.re;
+            ai[j] += cr * z.im;
+          }
+        } else {
+          const int jb = 1 << (a - kLog);
+#pragma unroll
+          for (int j = 0; j < G; ++j) {
+            if ((g + j) & jb) dg[j] -= dl;
+            const cplx z = zi[(g + j) ^ jb];
+            ar[j] += cr * z.re;
+            ai[j] += cr * z.im;
+          }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < G; ++j) {
+        const cplx zs = zi[g + j];
+        kc[g + j] = times_minus_i(cmake(dg[j] * zs.re + ar[j], dg[j] * zs.im + ai[j]));
+        if (store && tm_vec < 0) kout[tid + (uint32_t)(g + j) * kT] = kc[g + j];
+      }
+      if (store && tm_vec >= 0) tmem_st4(tm_addr<E>(tm_vec, g), &kc[g]);
+    }
+    if (store && tm_vec >= 0) tmem_wait_st();
+  }
+
+  // ys = y + h * sum_j val[j] K[slot[j]]; with `carry` the last term's vector is `kc` (registers)
+  template <int E, int GC>
+  __device__ __forceinline__ void stage_carry(double h, int nnz, const int* slot, const double* val, cplx* const* kk,
+                                              const cplx* yy, cplx* out, const cplx (&kc)[E], bool carry) {
+    const uint32_t tid = threadIdx.x;
+    const int nl = carry ? nnz - 1 : nnz;
+#pragma unroll
+    for (int g = 0; g < E; g += GC) {
+      const uint32_t base = tid + (uint32_t)g * kT;
+      double sr[GC], si[GC];
+#pragma unroll
+      for (int e = 0; e < GC; ++e) sr[e] = si[e] = 0.0;
+      for (int j = 0; j < nl; ++j) {
+        const int sl = slot[j];
+        const int tm = tm_base != kNoTmem ? tmem_index_of_slot(sl) : -1;
+        const double v = val[j];
+        cplx kz[GC];
+        if (tm >= 0) {
+#pragma unroll
+          for (int e = 0; e < GC; e += 4) tmem_ld4(tm_addr<E>(tm, g + e), &kz[e]);
+        } else {
+          const cplx* kp = kk[sl] + base;
+#pragma unroll
+          for (int e = 0; e < GC; ++e) kz[e] = kp[e * kT];
+        }
+#pragma unroll
+        for (int e = 0; e < GC; ++e) {
+          sr[e] += v * kz[e].re;
+          si[e] += v * kz[e].im;
+        }
+      }
+      if (carry) {
+        const double v = val[nnz - 1];
+#pragma unroll
+        for (int e = 0; e < GC; ++e) {
+          sr[e] += v * kc[g + e].re;
+          si[e] += v * kc[g + e].im;
+        }
+      }
+      const cplx* yp = yy + base;
+      cplx* op = out + base;
+#pragma unroll
+      for (int e = 0; e < GC; ++e) {
+        const cplx yz = yp[e * kT];
+        op[e * kT] = cmake(yz.re + h * sr[e], yz.im + h * si[e]);
+      }
+    }
+  }
+
+  // final pass of a DOP853 step with ONE load per K vector for the three rows (b, e5, e3 share the slot list
+  // {k1, k6, ..., k12}); the last vector (k12) comes from `kc`.  ys_io := ynew.
+  template <int E>
+  __device__ __forceinline__ void final853_carry(double h, double atol, double rtol, cplx* const* kk, const cplx* yy,
+                                                 cplx* ys_io, const cplx (&kc)[E], double& err, double& err3,
+                                                 double& stden) {
+    constexpr int G = 4;
+    const uint32_t tid = threadIdx.x;
+    const int n = tables::DOP853_b_nnz[0];
+    const int* slot = tables::DOP853_b_slot[0];
+    const double *bv = tables::DOP853_b_val[0], *e5v = tables::DOP853_e5_val[0], *e3v = tables::DOP853_e3_val[0];
+#pragma unroll
+    for (int g = 0; g < E; g += G) {
+      const uint32_t base = tid + (uint32_t)g * kT;
+      double sr[G], si[G], e5r[G], e5i[G], e3r[G], e3i[G];
+#pragma unroll
+      for (int e = 0; e < G; ++e) sr[e] = si[e] = e5r[e] = e5i[e] = e3r[e] = e3i[e] = 0.0;
+      for (int j = 0; j < n - 1; ++j) {
+        const int sl = slot[j];
+        const int tm = tm_base != kNoTmem ? tmem_index_of_slot(sl) : -1;
+        const double b = bv[j], c5 = e5v[j], c3 = e3v[j];
+        cplx kz[G];
+        if (tm >= 0) {
+          tmem_ld4(tm_addr<E>(tm, g), kz);
+        } else {
+          const cplx* kp = kk[sl] + base;
+#pragma unroll
+          for (int e = 0; e < G; ++e) kz[e] = kp[e * kT];
+        }
+#pragma unroll
+        for (int e = 0; e < G; ++e) {
+          sr[e] += b * kz[e].re;
+          si[e] += b * kz[e].im;
+          e5r[e] += c5 * kz[e].re;
+          e5i[e] += c5 * kz[e].im;
+          e3r[e] += c3 * kz[e].re;
+          e3i[e] += c3 * kz[e].im;
+        }
+      }
+      {
+        const double b = bv[n - 1], c5 = e5v[n - 1], c3 = e3v[n - 1];
+#pragma unroll
+        for (int e = 0; e < G; ++e) {
+          const cplx kz = kc[g + e];
+          sr[e] += b * kz.re;
+          si[e] += b * kz.im;
+          e5r[e] += c5 * kz.re;
+          e5i[e] += c5 * kz.im;
+          e3r[e] += c3 * kz.re;
+          e3i[e] += c3 * kz.im;
+        }
+      }
+#pragma unroll
+      for (int e = 0; e < G; ++e) {
+        const uint32_t i = base + (uint32_t)e * kT;
+        const cplx yo = yy[i];
+        const cplx z = cmake(yo.re + h * sr[e], yo.im + h * si[e]);
+        double sk = atol + rtol * fmax(fabs(yo.re), fabs(z.re));
+        double q = e5r[e] / sk;
+        err += q * q;
+        q = e3r[e] / sk;
+        err3 += q * q;
+        sk = atol + rtol * fmax(fabs(yo.im), fabs(z.im));
+        q = e5i[e] / sk;
+        err += q * q;
+        q = e3i[e] / sk;
+        err3 += q * q;
+        const cplx old = ys_io[i];
+        const double dr = z.re - old.re, di = z.im - old.im;
+        stden += dr * dr + di * di;
+        ys_io[i] = z;
+      }
+    }
+  }
+
+  // One attempted DOP853 step with the register carry.  Needs the FIXED layout the kernel sets up for it
+  // (Workspace::fused_layout): y, ys and K slot 0 (k1) resident in shared memory under pointers that never
+  // move - the accepted solution is copied ys -> y by the thread that owns the elements and K4 = f(x+h, ynew) is
+  // written straight into slot 0, instead of the pointer swaps of step_dop853 (which would move y and k1
+  // between shared memory and the L2 workspace).  Same Butcher rows, same sums in the same order.
+  template <int E, class Ev>
+  __device__ __forceinline__ void step853_fused_impl(Ev& ev, int& accepted) {
+    constexpr int GC = 4;
+    Controller& c = ev.c;
+    const SolverOpts& o = ev.o;
+    const double x = c.x, h = c.h, tn = x + h;
+    const int64_t n_real = 2 * ev.P.dim;
+    auto stage_time = [=](int s) { return (s == 10) ? tn : x + tables::DOP853_c[s + 1] * h; };
+    ev.step_coefs(kCoefTab, stage_time);
+    cplx* const* vec = ev.w.vec;
+    cplx* const* kk = vec + kVecK;
+    const cplx* yy = vec[kVecY];
+    cplx* ys = vec[kVecYs];
+    const double* V = ev.V;
+    cplx kc[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) kc[e] = cmake(0.0, 0.0);
+#pragma unroll 1
+    for (int s = 0; s < 11; ++s) {
+      stage_carry<E, GC>(h, tables::DOP853_a_nnz[s], tables::DOP853_a_slot[s], tables::DOP853_a_val[s], kk, yy, ys, kc,
+                         s >= 1);
+      __syncthreads();
+      const int dst = (s == 9) ? 1 : (s == 10) ? 2 : s + 1;
+      // k2 (s = 0) is only ever read as the carried term of the next row: it is not stored
+      rhs_carry<E>(ev.w.coefs_tab[s], V, ys, kk[dst], kc, s != 0, tm_base != kNoTmem ? tmem_index_of_slot(dst) : -1);
+      __syncthreads();
+    }
+    c.nfcn += 11;
+    double err = 0.0, err3 = 0.0, stden = 0.0;
+    final853_carry<E>(h, o.atol, o.rtol, kk, yy, ys, kc, err, err3, stden);
+    sum3(err, err3, stden);  // its barriers also publish ys = ynew
+    accepted = c.decide(o, c.err_dop853(err, err3, n_real));
+    if (accepted) {
+      cplx* y = vec[kVecY];
+      const uint32_t tid = threadIdx.x;
+#pragma unroll
+      for (int e = 0; e < E; ++e) y[tid + (uint32_t)e * kT] = ys[tid + (uint32_t)e * kT];  // y = ynew (own elements)
+      rhs_carry<E>(ev.w.coefs_tab[10], V, ys, kk[0], kc, true);  // K4 = f(x+h, ynew) = next step's k1, into slot 0
+      c.nfcn += 1;
+      if (c.stiff_due(o)) {
+        const cplx* k12 = kk[2];
+        double stnum = 0.0;
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+          const cplx b = k12[tid + (uint32_t)e * kT];
+          const double dr = kc[e].re - b.re, di = kc[e].im - b.im;
+          stnum += dr * dr + di * di;
+        }
+        sum1(stnum);
+        c.stiff_update(o, stnum, stden);
+      }
+      __syncthreads();
+    }
+  }
+  template <class Ev>
+  __device__ __forceinline__ bool step853_fused(Ev& ev, int& accepted) {
+    if (kT == 0 || ev.w.coefs_tab == nullptr || ev.P.n_atoms > kMaxAtoms) return false;
+    const int e = exact_elems(ev.P.dim);
+    if (e == 8 && ev.P.n_atoms == kLog + 3) {
+      step853_fused_impl<8>(ev, accepted);
+      return true;
+    }
+    if (e == 4 && ev.P.n_atoms == kLog + 2) {
+      step853_fused_impl<4>(ev, accepted);
+      return true;
+    }
+    return false;
   }
 
   // kout = -i H(t) ys for a two-level full space with real coefficients (TaskEvolver::fast_rhs).  Same
@@ -385,6 +712,8 @@ struct SmallArgs {
   int n_vec;                    // vectors in use (12 for dop853, 9 for dopri5)
   int n_smem_vecs;              // how many of them (in priority order) live in shared memory
   int vec_order[kNumVec];       // priority order: vec_order[r] = vector index with rank r
+  int fused_layout;             // ranks 0..2 = ys, K slot 0, y are in shared memory: step853_fused may run
+  int use_tmem;                 // with it: K slots 3..6 in tensor memory (one CTA per SM, dim <= 4096)
 };
 
 // kMinCtas = 2: two tasks share an SM (two CTAs of 512 threads at dim 4096): while one task streams K vectors
@@ -399,9 +728,19 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) evolve_small_kernel(const 
   __shared__ cplx* s_vec[kNumVec];
   __shared__ int s_task;
 
+  __shared__ uint32_t s_tmem;
+
   CtaCtxT<kThreads> ctx;
   ctx.red = s_red;
   const int64_t dim = A.P.dim;
+  if (A.use_tmem) {  // uniform over the CTA
+    if (threadIdx.x < 32) tmem_alloc_all(&s_tmem);
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t warp = threadIdx.x >> 5, per_thread = 16u * (uint32_t)(dim / kThreads);
+    ctx.tm_base = s_tmem + ((32u * (warp & 3u)) << 16) + (warp >> 2) * per_thread;
+  }
   cplx* smem_vecs = reinterpret_cast<cplx*>(dyn_smem);
   cplx* my_gws = A.gws + (int64_t)blockIdx.x * A.gws_stride;
 
@@ -448,6 +787,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) evolve_small_kernel(const 
     w.vec = s_vec;
     w.coefs = &s_coefs;
     w.coefs_tab = s_tab;
+    w.fused_layout = A.fused_layout != 0;
     TaskEvolver<CtaCtxT<kThreads>> ev(ctx, A.P, rec, V, w, A.o);
 
     double t_cur = 0.0;
@@ -478,6 +818,11 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) evolve_small_kernel(const 
       if (threadIdx.x == 0 && A.stats) A.stats[(int64_t)task * A.n_times + k] = st;
     }
     __syncthreads();
+  }
+  if (A.use_tmem) {
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (threadIdx.x < 32) tmem_free_all(s_tmem);
   }
 }
 

@@ -1,0 +1,3 @@
+// bqa_small_k512.cu - translation unit of evolve_small_kernel<512, 1> (see bqa_small_launch.h)
+#include "bqa_small_kernel_impl.cuh"
+BQA_SMALL_INSTANTIATE(512, 1)
