@@ -453,6 +453,9 @@ def gpu_arm(args):
     torch.cuda.set_device(local_rank)
     dist = None
     if world > 1:
+        # NCCL writes its version banner to stdout at NCCL_DEBUG=VERSION/INFO; stdout carries the JSON line only
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO", "TRACE") and not os.environ.get("BQA_KEEP_NCCL_DEBUG"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         import torch.distributed as dist
 
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -644,7 +647,9 @@ def gpu_arm(args):
     roofline = {
         "kernel": "evolve_small_kernel (CTA-per-task DOP853: all stage combines, fused H(t) psi and error norms)",
         "bound": "hbm", "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
-        "peak_kind": peak_kind + " copy bandwidth", "traffic": evo.get("dram_bytes_per_bench_launch"),
+        "peak_kind": peak_kind + " copy bandwidth",
+        # DRAM bytes per RHS evaluation from the committed ncu capture of this kernel x the RHS evaluations of the launch
+        "traffic": (evo["dram_bytes_per_rhs"] * nfcn_total) if "dram_bytes_per_rhs" in evo else None,
         "traffic_source": evo.get("source"),
         "algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": kms, "share_of_step": kern_ms / dev_ms,
         "rhs_evals_per_launch": nfcn_total,
