@@ -39,7 +39,7 @@ class SpaceDesc(Structure):
 
 class SolverOpts(Structure):
     _fields_ = [("solver", c_int32), ("interaction_picture", c_int32), ("atol", c_double), ("rtol", c_double),
-                ("nsteps", c_int64), ("reject_mode", c_int32), ("engine", c_int32)]
+                ("nsteps", c_int64), ("reject_mode", c_int32), ("engine", c_int32), ("t_start", c_double)]
 
 
 class ShardDesc(Structure):
@@ -135,7 +135,7 @@ def _ptr(a) -> c_void_p:
 
 
 def make_opts(solver_name="dop853", atol=1e-7, rtol=1e-14, nsteps=2_147_483_647, interaction_picture=False,
-              reject_mode=1, engine="auto") -> SolverOpts:
+              reject_mode=1, engine="auto", t_start=0.0) -> SolverOpts:
     if solver_name == "lsoda":
         raise NotImplementedError(
             "solver 'lsoda' has no GPU implementation in the B200 backend (and there is no CPU fallback); "
@@ -144,7 +144,7 @@ def make_opts(solver_name="dop853", atol=1e-7, rtol=1e-14, nsteps=2_147_483_647,
     if solver_name not in SOLVERS:
         raise ValueError(f"'{solver_name}' not supported.")
     return SolverOpts(SOLVERS[solver_name], int(bool(interaction_picture)), float(atol), float(rtol), int(nsteps),
-                      int(reject_mode), ENGINES[engine] if isinstance(engine, str) else int(engine))
+                      int(reject_mode), ENGINES[engine] if isinstance(engine, str) else int(engine), float(t_start))
 
 
 class Plan:

@@ -156,6 +156,7 @@ static int evolve_small_device(bqa_plan* p, const double* d_records, const int64
   A.stats = d_stats;
   A.o = default_opts(o->solver, o->atol, o->rtol, o->nsteps, o->interaction_picture);
   A.o.reject_mode = o->reject_mode;
+  A.t_start = o->t_start;
   const bool d5 = o->solver == BQA_SOLVER_DOPRI5;
   A.n_vec = d5 ? 9 : 12;
   // the fused step needs: dop853, two-level full space, no CSR term, Schroedinger picture (the device also checks
@@ -206,6 +207,7 @@ static int check_opts(const bqa_solver_opts* o) {
   if (o->solver != BQA_SOLVER_DOPRI5 && o->solver != BQA_SOLVER_DOP853)
     return fail("solver %d not supported (dop853 = 8, dopri5 = 5; lsoda has no GPU implementation)", o->solver);
   if (!(o->atol >= 0.0) || !(o->rtol >= 0.0) || (o->atol == 0.0 && o->rtol == 0.0)) return fail("bad tolerances");
+  if (!(o->t_start == o->t_start) || o->t_start < 0.0) return fail("bad t_start");
   return 0;
 }
 

@@ -161,7 +161,7 @@ template <class Integrator>
 __device__ __forceinline__ void cluster_run_times(Integrator& I, TaskEvolver<ClusterCtx>& ev, const SmallArgs& A, int task,
                                                   int rank) {
   const int64_t dim = A.P.dim;
-  double t_cur = 0.0;
+  double t_cur = A.t_start;
   bool failed = false;
   for (int k = 0; k < A.n_times; ++k) {
     const double t_next = A.times[(int64_t)task * A.n_times + k];

@@ -191,7 +191,7 @@ static int evolve_large_run(bqa_plan* p, LgScratch& X, const double* d_records, 
       const cplx* src = d_psi0 + (psi0_mode == 2 ? (int64_t)task * dim : 0);
       cudaMemcpyAsync(hc.vec[kVecY], src, sizeof(cplx) * dim, cudaMemcpyDeviceToDevice, s);
     }
-    double t_cur = 0.0;
+    double t_cur = o->t_start;
     bool failed = false;
     for (int k = 0; k < n_times; ++k) {
       const double t_next = h_times[(size_t)task * n_times + k];

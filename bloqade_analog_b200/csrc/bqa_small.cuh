@@ -714,6 +714,7 @@ struct SmallArgs {
   int vec_order[kNumVec];       // priority order: vec_order[r] = vector index with rank r
   int fused_layout;             // ranks 0..2 = ys, K slot 0, y are in shared memory: step853_fused may run
   int use_tmem;                 // with it: K slots 3..6 in tensor memory (one CTA per SM, dim <= 4096)
+  double t_start;               // time of the initial state (bqa_solver_opts::t_start)
 };
 
 // kMinCtas = 2: two tasks share an SM (two CTAs of 512 threads at dim 4096): while one task streams K vectors
@@ -790,7 +791,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) evolve_small_kernel(const 
     w.fused_layout = A.fused_layout != 0;
     TaskEvolver<CtaCtxT<kThreads>> ev(ctx, A.P, rec, V, w, A.o);
 
-    double t_cur = 0.0;
+    double t_cur = A.t_start;
     bool failed = false;
     for (int k = 0; k < A.n_times; ++k) {
       const double t_next = A.times[(int64_t)task * A.n_times + k];

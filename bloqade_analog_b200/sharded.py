@@ -10,6 +10,8 @@ carries the 64-byte IPC handles at set-up and a few scalars (norms, sampling pre
 """
 from __future__ import annotations
 
+import json
+import os
 from typing import List, Optional, Sequence
 
 import numpy as np
@@ -121,11 +123,12 @@ class ShardedHamiltonian:
 
     # ---- AnalogGate._apply (state_vector.py:574-602) ---------------------------------------------------------------
     def evolve(self, times: Sequence[float] = (), psi0_local=None, solver_name: str = "dop853", atol: float = 1e-7,
-               rtol: float = 1e-14, nsteps: int = 2_147_483_647, reject_mode: int = 1):
-        """returns (states [n_times, local_dim] complex128 on this GPU, stats); collective"""
+               rtol: float = 1e-14, nsteps: int = 2_147_483_647, reject_mode: int = 1, t_start: float = 0.0):
+        """returns (states [n_times, local_dim] complex128 on this GPU, stats); collective.  `t_start` is the time of
+        `psi0_local` (resume from a checkpoint, see `evolve_checkpointed`)"""
         torch, dist = self._torch, self._dist
         times = np.asarray(list(times) if len(times) else [self.program.duration], dtype=np.float64)
-        opts = _lib.make_opts(solver_name, atol, rtol, nsteps, False, reject_mode, "streamed")
+        opts = _lib.make_opts(solver_name, atol, rtol, nsteps, False, reject_mode, "streamed", t_start)
         out = torch.empty((times.size, self.local_dim), dtype=torch.complex128, device=f"cuda:{self.device}")
         p0 = None if psi0_local is None else int(psi0_local.contiguous().data_ptr())
         _lib.shard_reset(self._sync)  # barrier counters / abort word back to zero, ranks in step again
@@ -133,6 +136,61 @@ class ShardedHamiltonian:
         stats = self.plan.evolve_sharded(self.record, opts, self.desc, times, out.data_ptr(), p0)
         dist.barrier(group=self.group)
         return out, stats
+
+    # ---- mid-run checkpoints (the reference only serialises finished batches, serialize.py:115-213) --
+    def checkpoint_path(self, directory: str) -> str:
+        return os.path.join(directory, f"shard_{self.rank:02d}_of_{self.world:02d}.npy")
+
+    def save_checkpoint(self, directory: str, t: float, psi_local) -> None:
+        """this rank's shard -> `directory`/shard_RR_of_WW.npy, then (rank 0, after every rank has written) meta.json;
+        a resume only trusts a directory whose meta.json exists, so a crash mid-write leaves the previous one valid"""
+        os.makedirs(directory, exist_ok=True)
+        tmp = self.checkpoint_path(directory) + ".tmp.npy"
+        np.save(tmp, psi_local.detach().cpu().numpy())
+        os.replace(tmp, self.checkpoint_path(directory))
+        self._dist.barrier(group=self.group)
+        if self.rank == 0:
+            meta = {"t": float(t), "world": self.world, "n_atoms": self.n_atoms, "local_dim": self.local_dim,
+                    "duration": float(self.program.duration)}
+            with open(os.path.join(directory, "meta.json.tmp"), "w") as f:
+                json.dump(meta, f)
+            os.replace(os.path.join(directory, "meta.json.tmp"), os.path.join(directory, "meta.json"))
+        self._dist.barrier(group=self.group)
+
+    def load_checkpoint(self, directory: str):
+        """(t, psi_local on this GPU) of the checkpoint in `directory`, or None when there is no complete one"""
+        meta_file = os.path.join(directory, "meta.json")
+        if not os.path.exists(meta_file):
+            return None
+        with open(meta_file) as f:
+            meta = json.load(f)
+        if meta["world"] != self.world or meta["n_atoms"] != self.n_atoms:
+            raise ValueError("checkpoint was written for another register / number of GPUs")
+        psi = self._torch.from_numpy(np.load(self.checkpoint_path(directory))).to(f"cuda:{self.device}")
+        return float(meta["t"]), psi
+
+    def evolve_checkpointed(self, directory: str, every: float, **solver):
+        """AnalogGate._apply to the end of the program with a checkpoint every `every` microseconds of program time;
+        resumes from `directory` when it holds a complete checkpoint.  SciPy's ode restarts the integrator at every
+        output time (state_vector.py:589-600), so the segments ARE the reference's flow for times = the checkpoint
+        grid: an interrupted and resumed run ends bit for bit like an uninterrupted one with the same grid.
+        Returns (final shard, list of per-segment stats)."""
+        duration = float(self.program.duration)
+        grid = [min(duration, every * k) for k in range(1, int(np.ceil(duration / every)) + 1)]
+        t, psi, all_stats = 0.0, None, []
+        loaded = self.load_checkpoint(directory)
+        if loaded is not None:
+            t, psi = loaded
+        for t_next in grid:
+            if t_next <= t:
+                continue
+            states, stats = self.evolve([t_next], psi0_local=psi, t_start=t, **solver)
+            all_stats.append(stats)
+            if int(stats["status"][0]) != 1:
+                raise RuntimeError(f"sharded evolve failed with status {int(stats['status'][0])} in ({t}, {t_next}]")
+            t, psi = t_next, states[0]
+            self.save_checkpoint(directory, t, psi)
+        return psi, all_stats
 
     # ---- StateVector.norm / sample (state_vector.py:210-217, space.py:211-229) ----------------------------------------
     def norm2_shards(self, psi_local) -> np.ndarray:

@@ -71,6 +71,10 @@ typedef struct {
                                   Python-side default: same step sequence and failure codes as the
                                   oracle), 0 = Hairer dop853.f / SciPy <= 1.16 (fewer steps)         */
   int32_t engine;              /* BQA_ENGINE_*                                                       */
+  double t_start;              /* time of psi0 (0 in the reference's flow).  Non-zero: resume of a run that was
+                                  checkpointed at an output time - SciPy's ode restarts the integrator at every
+                                  output time (state_vector.py:589-600), so evolving to t1, saving the state and
+                                  resuming with t_start = t1 continues bit for bit like the uninterrupted run    */
 } bqa_solver_opts;
 
 typedef struct {

@@ -32,7 +32,7 @@ def test_library_loads_and_exports_every_declared_symbol():
 
 def test_struct_layouts_match_header():
     assert ctypes.sizeof(_lib.SpaceDesc) == 32
-    assert ctypes.sizeof(_lib.SolverOpts) == 40
+    assert ctypes.sizeof(_lib.SolverOpts) == 48 and _lib.SolverOpts.t_start.offset == 40
     assert ctypes.sizeof(_lib.TaskStats) == 56
     assert _lib.STATS_DTYPE.itemsize == ctypes.sizeof(_lib.TaskStats)
 

@@ -273,3 +273,53 @@ def test_call_signature_and_errors_like_reference(ref, b200):
         r.run(10, multiprocessing=True, cache_matrices=True)
     with pytest.raises(NotImplementedError):
         r.run(10, solver_name="lsoda")
+
+
+def _fn_programs():
+    """the `.fn(...)` programs of the reference's tests/test_python_codegen.py:270-286 and tests/test_python_emulator.py:85,
+    and a Gaussian-smoothed drive"""
+    from bloqade.analog import piecewise_linear, start
+    from bloqade.analog.ir.control.waveform import GaussianKernel
+
+    def phase_function(t):
+        return np.sin(t)
+
+    p1 = (start.add_position([(0, 0), (0, 6)])
+          .rydberg.detuning.uniform.piecewise_linear([0.1, 0.8, 0.1], [-10, -10, 20, 20])
+          .amplitude.uniform.piecewise_linear([0.1, 0.8, 0.1], [0, 15.7, 15.7, 0])
+          .phase.location(0, 1.0).fn(phase_function, 1.0)
+          .detuning.scale([0.1, 1.0]).piecewise_constant([0.1, 0.3, 0.1], [0, 1, 2]).poly([2, -1, 3, -4], 0.5))
+    p2 = (start.add_position((0, 0)).add_position((0, 6.0))
+          .rydberg.detuning.uniform.piecewise_linear([0.1, 1.0, 0.1], [-20, -20, 20, 20])
+          .amplitude.uniform.piecewise_linear([0.1, 1.0, 0.1], [0, 10, 10, 0])
+          .amplitude.location(1).fn(lambda t: 4 * np.sin(3 * t), 1.2))
+    smooth = piecewise_linear([0.1, 0.4, 0.1], [0, 12, 12, 0]).smooth(0.05, GaussianKernel)
+    p3 = (start.add_position([(0, 0), (0, 6.2), (6.2, 0)])
+          .rydberg.rabi.amplitude.uniform.apply(smooth)
+          .detuning.uniform.piecewise_linear([0.1, 0.4, 0.1], [-12, -12, 14, 14]))
+    return [("codegen_fn_phase", p1, 1e-8), ("emulator_fn_amplitude", p2, 1e-8), ("gaussian_smooth", p3, 1e-5)]
+
+
+@pytest.mark.parametrize("which", [0, 1, 2])
+def test_python_fn_and_smooth_waveforms_match_reference(ref, which):
+    """PythonFn / Smooth waveforms (waveform.py:405-468,571-642) are lowered to a cubic-Hermite table for the device
+    (tests/test_pyfn_lowering.py holds the table-vs-interpreter bounds); final states of run_callback against the
+    reference's own integration: infidelity < 1e-8 for `.fn(...)` drives.  A Smooth waveform is evaluated by the
+    reference with quad(epsabs=1e-4): its H(t) jitters by ~2e-3 rad/us from one RHS call to the next, the table
+    interpolates between its knots, so the two answers are only comparable to ~(dOmega T)^2: bound 1e-5."""
+    from bloqade_analog_b200 import routine
+
+    name, program, bound = _fn_programs()[which]
+
+    def collect(state, metadata, hamiltonian):
+        return state.data.copy()
+
+    (old,) = program.bloqade.python().run_callback(collect, atol=1e-10, rtol=1e-10)
+    routine.install()
+    try:
+        r_new = program.bloqade.python()
+        assert type(r_new).__name__ == "BloqadeB200Routine"
+        (new,) = r_new.run_callback(collect, atol=1e-10, rtol=1e-10)
+    finally:
+        routine.uninstall()
+    assert infidelity(old, new) < bound, name

@@ -376,6 +376,24 @@ def test_output_times_after_a_failure_are_marked(engine):
     assert [int(x) for x in st["status"]] == [1, -2, -1], st["status"]
 
 
+@pytest.mark.parametrize("engine", ["cta", "cluster", "streamed"])
+def test_resume_from_an_output_time_is_bit_identical(engine):
+    """bqa_solver_opts::t_start: evolve to t1, take the state, resume from (t1, state) to T == evolve with
+    times = [t1, T] (SciPy's ode restarts at every output time, state_vector.py:589-600) - the mid-run checkpoint
+    of the streamed / sharded engines rests on this"""
+    h = ham("c1_square3_a6p5_short")
+    d = h.emulator_ir.duration
+    blob, offsets = lowering.concat_records([h.record])
+    o = _lib.make_opts("dop853", 1e-7, 1e-14, engine=engine)
+    both, st = h.plan.evolve_batch(blob, offsets, np.array([[0.4 * d, d]]), o)
+    first, _ = h.plan.evolve_batch(blob, offsets, np.array([[0.4 * d]]), o)
+    assert np.array_equal(first[0, 0], both[0, 0])
+    o2 = _lib.make_opts("dop853", 1e-7, 1e-14, engine=engine, t_start=0.4 * d)
+    rest, st2 = h.plan.evolve_batch(blob, offsets, np.array([[d]]), o2, psi0=first[0, 0])
+    assert np.array_equal(rest[0, 0], both[0, 1])
+    assert int(st2["nfcn"][0, 0]) == int(st["nfcn"][0, 1]) and int(st2["status"][0, 0]) == 1
+
+
 def test_gate_run_seeded_matches_reference_shots():
     c, h = golden_case("c1_square3_a6p5_short"), ham("c1_square3_a6p5_short")
     import zlib
@@ -612,8 +630,11 @@ def test_sharded_evolve_two_gpus_matches_unsharded():
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
     assert lines, out.stderr[-2000:]
-    res = json.loads(lines[-1])
+    res = {}
+    for l in lines:
+        res.update(json.loads(l))
     assert res["stats"]["status"] == 1
     assert res["apply_max_rel_err"] < 1e-13
     assert res["infidelity"] < 1e-8
     assert res["shots_rows_differing"] <= 1
+    assert res["checkpoint_resume_bit_identical"] and res["segments_resumed"] == 2
