@@ -317,6 +317,31 @@ def hpsi_roofline(torch, device_index, peaks, peak_kind, n_atoms=25, reps=20):
            "frac_of_8TBps_nominal": ach / 8000.0, "peak_kind": peak_kind + " burst copy", "algorithmic_bytes_per_launch": alg,
            "ms_per_launch_median": float(np.median(ms)), "ms_per_launch_min": float(ms.min()),
            "traffic": traffic["bytes"] if traffic else None, "traffic_source": traffic["source"] if traffic else None}
+    # kernels (3) and (4) on the same state: norm (16*D read) and Born sampling of 1000 shots (16*D read; the
+    # two-level form for large states writes no CDF array)
+    shots = 1000
+    uni = torch.rand(shots, dtype=torch.float64, device="cuda")
+    sh = torch.empty(shots, n_atoms, dtype=torch.uint8, device="cuda")
+    nrm = torch.empty(1, dtype=torch.float64, device="cuda")
+
+    def t_med(fn, reps=10):
+        fn()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+        torch.cuda.synchronize()
+        for a, b in ev:
+            a.record(stream)
+            fn()
+            b.record(stream)
+        torch.cuda.synchronize()
+        return float(np.median([a.elapsed_time(b) for a, b in ev]))
+
+    ms_n = t_med(lambda: h.plan.norm_noalloc(psi.data_ptr(), 1, nrm.data_ptr()))
+    ms_s = t_med(lambda: h.plan.sample(psi.data_ptr(), uni.data_ptr(), mem=D, n_states=1, n_shots=shots, shots_out=sh.data_ptr()))
+    res["reductions"] = {
+        "norm": {"ms": ms_n, "algorithmic_bytes": 16.0 * dim, "achieved": 16.0 * dim / ms_n / 1e6, "unit": "GB/s",
+                 "frac": 16.0 * dim / ms_n / 1e6 / peaks["hbm_gbs"]},
+        "sample_1000_shots": {"ms": ms_s, "algorithmic_bytes": 16.0 * dim, "achieved": 16.0 * dim / ms_s / 1e6, "unit": "GB/s",
+                              "frac": 16.0 * dim / ms_s / 1e6 / peaks["hbm_gbs"]}}
     h.plan.close()
     del psi, out
     torch.cuda.empty_cache()

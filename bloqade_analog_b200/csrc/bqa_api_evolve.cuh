@@ -332,8 +332,11 @@ int bqa_run_batch(bqa_plan* p, const double* records, const int64_t* offsets, in
     double* n2 = partial + (size_t)blocks * n_tasks;
     int rc = norm2_segments(p, (const cplx*)psi.dev, n_tasks, partial, blocks, n2);
     if (!rc) {
-      scale_by_norm_kernel<<<dim3(blocks, n_tasks), 256, 0, p->stream>>>((cplx*)psi.dev, dim, dim, n2);
-      LAUNCHED();
+      for (int s0 = 0; s0 < n_tasks; s0 += kMaxSegPerLaunch) {
+        const int ns = std::min(kMaxSegPerLaunch, n_tasks - s0);
+        scale_by_norm_kernel<<<dim3(blocks, ns), 256, 0, p->stream>>>((cplx*)psi.dev + (size_t)s0 * dim, dim, dim, n2 + s0);
+        LAUNCHED();
+      }
       rc = sample_device(p, (const cplx*)psi.dev, n_tasks, (const double*)un.dev, n_shots, project, (uint8_t*)sh.dev);
     }
     cudaError_t e = cudaStreamSynchronize(p->stream);

@@ -7,11 +7,18 @@ static int grid_for(const bqa_plan* p, int64_t n, int threads, int per_sm = 8) {
   return (int)std::max<int64_t>(1, std::min(want, cap));
 }
 
+// gridDim.y is limited to 65535: batched segment kernels are launched in chunks of this many segments
+constexpr int kMaxSegPerLaunch = 65535;
+
 // segment-wise |psi|^2 sums -> d_out[n_seg] (two deterministic passes)
 static int norm2_segments(bqa_plan* p, const cplx* d_psi, int n_seg, double* d_partial, int blocks, double* d_out) {
-  dim3 g(blocks, n_seg);
-  norm2_partial_kernel<<<g, 256, 0, p->stream>>>(d_psi, p->P.dim, p->P.dim, d_partial);
-  LAUNCHED();
+  const int64_t dim = p->P.dim;
+  for (int s0 = 0; s0 < n_seg; s0 += kMaxSegPerLaunch) {
+    const int ns = std::min(kMaxSegPerLaunch, n_seg - s0);
+    dim3 g(blocks, ns);
+    norm2_partial_kernel<<<g, 256, 0, p->stream>>>(d_psi + (size_t)s0 * dim, dim, dim, d_partial + (size_t)s0 * blocks);
+    LAUNCHED();
+  }
   finish_sum_kernel<<<n_seg, 256, 0, p->stream>>>(d_partial, blocks, 1, d_out);
   LAUNCHED();
   CK(cudaGetLastError());
@@ -23,24 +30,45 @@ static int sample_device(bqa_plan* p, const cplx* d_psi, int n_seg, const double
                          int project, uint8_t* d_shots) {
   const int64_t dim = p->P.dim;
   const int n_tiles = (int)((dim + kScanTile - 1) / kScanTile);
+  // large states with few shots: no CDF array, each shot re-evaluates one tile (sample_search_tiles_kernel)
+  const bool two_level = dim >= ((int64_t)1 << 18) && (int64_t)n_shots * kScanTile * 2 <= dim;
   void* sc = nullptr;
-  size_t need = sizeof(double) * ((size_t)n_seg * n_tiles + n_seg + (size_t)n_seg * dim);
+  size_t need = sizeof(double) * ((size_t)n_seg * n_tiles + n_seg + (two_level ? 0 : (size_t)n_seg * dim));
   if (plan_scratch(p, need, &sc)) return 1;
   double* tile_sums = (double*)sc;
   double* totals = tile_sums + (size_t)n_seg * n_tiles;
   double* cdf = totals + n_seg;
-  dim3 g(n_tiles, n_seg);
-  scan_tile_sums_kernel<<<g, kScanThreads, 0, p->stream>>>(d_psi, dim, dim, n_tiles, tile_sums);
-  LAUNCHED();
+  const int project_flag = (project && p->P.n_level == 3) ? 1 : 0;
+  for (int s0 = 0; s0 < n_seg; s0 += kMaxSegPerLaunch) {
+    const int ns = std::min(kMaxSegPerLaunch, n_seg - s0);
+    dim3 g(n_tiles, ns);
+    scan_tile_sums_kernel<<<g, kScanThreads, 0, p->stream>>>(d_psi + (size_t)s0 * dim, dim, dim, n_tiles,
+                                                            tile_sums + (size_t)s0 * n_tiles);
+    LAUNCHED();
+  }
   scan_tile_offsets_kernel<<<n_seg, 1024, 0, p->stream>>>(tile_sums, n_tiles, totals);
   LAUNCHED();
-  scan_write_cdf_kernel<<<g, kScanThreads, 0, p->stream>>>(d_psi, dim, dim, n_tiles, tile_sums, totals, cdf);
-  LAUNCHED();
-  dim3 gs((n_shots + 127) / 128, n_seg);
-  const int project_flag = (project && p->P.n_level == 3) ? 1 : 0;
-  sample_search_kernel<<<gs, 128, 0, p->stream>>>(cdf, dim, p->P.configs, p->P.n_atoms, p->P.n_level, project_flag,
-                                                  d_uniforms, n_shots, d_shots);
-  LAUNCHED();
+  for (int s0 = 0; s0 < n_seg; s0 += kMaxSegPerLaunch) {
+    const int ns = std::min(kMaxSegPerLaunch, n_seg - s0);
+    const cplx* psi0 = d_psi + (size_t)s0 * dim;
+    const double* uni0 = d_uniforms + (size_t)s0 * n_shots;
+    uint8_t* shots0 = d_shots + (size_t)s0 * n_shots * p->P.n_atoms;
+    if (two_level) {
+      sample_search_tiles_kernel<<<dim3(n_shots, ns), kScanThreads, 0, p->stream>>>(
+          psi0, dim, dim, n_tiles, tile_sums + (size_t)s0 * n_tiles, totals + s0, p->P.configs, p->P.n_atoms, p->P.n_level,
+          project_flag, uni0, n_shots, shots0);
+      LAUNCHED();
+      continue;
+    }
+    dim3 g(n_tiles, ns);
+    scan_write_cdf_kernel<<<g, kScanThreads, 0, p->stream>>>(psi0, dim, dim, n_tiles, tile_sums + (size_t)s0 * n_tiles,
+                                                            totals + s0, cdf + (size_t)s0 * dim);
+    LAUNCHED();
+    dim3 gs((n_shots + 127) / 128, ns);
+    sample_search_kernel<<<gs, 128, 0, p->stream>>>(cdf + (size_t)s0 * dim, dim, p->P.configs, p->P.n_atoms, p->P.n_level,
+                                                    project_flag, uni0, n_shots, shots0);
+    LAUNCHED();
+  }
   CK(cudaGetLastError());
   return 0;
 }

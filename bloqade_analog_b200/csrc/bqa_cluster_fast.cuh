@@ -27,6 +27,7 @@
 namespace bqa {
 
 constexpr int kVecYsB = 12;  // 13th vector of the fast path: second stage-input buffer
+constexpr int kWfCache = 64;  // waveforms of a task the service warp evaluates one per lane
 
 // Butcher rows in the constant bank (uniform LDC instead of L1-flushed global loads)
 namespace ctab {
@@ -90,6 +91,7 @@ struct Fast853 {
   uint32_t* addr_gen;   // the u32 address table as a generic pointer (for the swaps)
   Coefs* coefs;         // shared [2]
   int* realflag;        // shared [2]: all drive coefficients of coefs[b] are real
+  double* wfval;        // shared [kWfCache]: waveform values of the service warp
   const SolverOpts& o;
   Controller& c;
   int n, tid;
@@ -255,10 +257,21 @@ struct Fast853 {
   }
 
   // service warp: coefficient table of time t into buffer b (+ its "all real" flag)
+  // Every waveform of the task is evaluated once, one per lane (wf_eval is a dependent chain of ~700 cycles; a lane
+  // per ATOM repeated it for every term, which made this warp the critical path of a stage at dim <= 1024); then a
+  // lane per atom combines the values.  Same functions, same order: the same bits as coef_entry.
   __device__ __forceinline__ void service_coefs(int b, double t) {
     const int a = tid - T;
     bool im = false;
-    if (a < n) {
+    if (tv.n_wf <= kWfCache) {
+      for (int w = a; w < tv.n_wf; w += 32) wfval[w] = wf_eval(tv, w, t);
+      __syncwarp();
+      if (a < n) {
+        coef_entry_from_values(tv, wfval, a, coefs[b]);
+        im = coefs[b].c_im[0][a] != 0.0;
+      }
+      __syncwarp();
+    } else if (a < n) {
       coef_entry(tv, t, a, coefs[b]);
       im = coefs[b].c_im[0][a] != 0.0;
     }
@@ -477,6 +490,7 @@ __global__ void __launch_bounds__(544, 1) evolve_cluster_kernel(const ClusterArg
   extern __shared__ __align__(16) unsigned char dyn_smem[];
   __shared__ Coefs s_coefs[2];
   __shared__ int s_real[2];
+  __shared__ double s_wfval[kWfCache];
   __shared__ uint32_t s_addr[kNumVec + 1];  // shared address of every vector's chunk (fast path)
   __shared__ double s_red[3 * 32];
   __shared__ double s_part[8];
@@ -556,7 +570,7 @@ __global__ void __launch_bounds__(544, 1) evolve_cluster_kernel(const ClusterArg
       const int tid = (int)threadIdx.x;
 #define BQA_FAST_CASE(KK, TT)                                                                               \
   {                                                                                                         \
-    Fast853<KK, TT> fe{ctx, ev, A.P, ev.tv, s_vec, s_addr, s_coefs, s_real, ev.o, ev.c, A.P.n_atoms, tid,   \
+    Fast853<KK, TT> fe{ctx, ev, A.P, ev.tv, s_vec, s_addr, s_coefs, s_real, s_wfval, ev.o, ev.c, A.P.n_atoms, tid, \
                        tid < TT, smem_u32(smem_vecs), smem_u32(s_addr), smem_u32(s_coefs),                  \
                        V ? smem_u32(Vs) : 0u, {0u, 0u, 0u}, 0, 0};                                          \
     fe.init_peers();                                                                                        \

@@ -197,6 +197,43 @@ BQA_HD void coef_entry(const TaskView& tv, double t, int e, Coefs& out) {
   out.c_im[s][a] = ci;
 }
 
+// coef_entry with the waveform values at time t already evaluated (wfv[w] = wf_eval(tv, w, t) for every waveform of
+// the task): the same sums in the same order, so the same bits.  Lets a warp evaluate every waveform ONCE, one per
+// lane, instead of once per atom.
+BQA_HD void coef_entry_from_values(const TaskView& tv, const double* wfv, int e, Coefs& out) {
+  int n = tv.n_atoms;
+  int s = e / n, a = e - s * n;
+  double d = 0.0, cr = 0.0, ci = 0.0;
+  int dstride = 2 + n, rstride = 3 + n;
+  for (int k = 0; k < tv.n_det; ++k) {
+    const double* r = tv.det + (int64_t)k * dstride;
+    if ((int)r[1] != s) continue;
+    double sc = r[2 + a];
+    if (sc == 0.0) continue;
+    d += wfv[(int)r[0]] * sc;
+  }
+  for (int k = 0; k < tv.n_rabi; ++k) {
+    const double* r = tv.rabi + (int64_t)k * rstride;
+    if ((int)r[2] != s) continue;
+    double sc = r[3 + a];
+    if (sc == 0.0) continue;
+    double amp = wfv[(int)r[0]] * 0.5;
+    int pw = (int)r[1];
+    if (pw >= 0) {
+      double ph = wfv[pw];
+      double sn, cs;
+      sincos(ph, &sn, &cs);
+      cr += amp * cs * sc;   // amp * exp(-i ph)
+      ci -= amp * sn * sc;
+    } else {
+      cr += amp * sc;
+    }
+  }
+  out.delta[s][a] = d;
+  out.c_re[s][a] = cr;
+  out.c_im[s][a] = ci;
+}
+
 BQA_HD void coef_csr_entry(const PlanView& P, const TaskView& tv, double t, int k, Coefs& out) {
   const CsrTerm& T = P.csr[k];
   double amp = wf_eval(tv, T.amp_wf, t) * 0.5;

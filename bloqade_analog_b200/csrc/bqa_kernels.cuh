@@ -176,62 +176,72 @@ constexpr int kScanThreads = 256;
 constexpr int kScanItems = 8;
 constexpr int kScanTile = kScanThreads * kScanItems;  // 2048 probabilities per CTA
 
-// tile_sums[seg][tile] = sum of |psi|^2 over the tile
+// tile_sums[seg][tile] = sum of |psi|^2 over the tile (coalesced: a warp reads 512 contiguous bytes per load)
 __global__ void __launch_bounds__(kScanThreads)
 scan_tile_sums_kernel(const cplx* __restrict__ psi, int64_t dim, int64_t seg_stride, int n_tiles, double* tile_sums) {
   __shared__ double red[32];
   const cplx* p = psi + (int64_t)blockIdx.y * seg_stride;
-  const int64_t base = (int64_t)blockIdx.x * kScanTile;
-  double s = 0.0;
+  const int64_t base = (int64_t)blockIdx.x * kScanTile + threadIdx.x;
+  cplx z[kScanItems];
+#pragma unroll
   for (int k = 0; k < kScanItems; ++k) {
-    int64_t i = base + (int64_t)threadIdx.x * kScanItems + k;
-    if (i < dim) {
-      cplx z = p[i];
-      s += z.re * z.re + z.im * z.im;
-    }
+    const int64_t i = base + (int64_t)k * kScanThreads;
+    z[k] = i < dim ? p[i] : cmake(0.0, 0.0);
   }
+  double s = 0.0;
+#pragma unroll
+  for (int k = 0; k < kScanItems; ++k) s += z[k].re * z[k].re + z[k].im * z[k].im;
   s = block_sum(s, red);
   if (threadIdx.x == 0) tile_sums[(int64_t)blockIdx.y * n_tiles + blockIdx.x] = s;
 }
 
-// exclusive scan of tile_sums per segment (one CTA per segment, sequential over chunks); totals[seg]
+// exclusive scan of tile_sums per segment (one CTA per segment, chunks of 1024 tiles: warp-shuffle scans + a scan of
+// the 32 warp totals); totals[seg]
 __global__ void __launch_bounds__(1024)
 scan_tile_offsets_kernel(double* tile_sums, int n_tiles, double* totals) {
-  __shared__ double buf[1024];
+  __shared__ double wtot[32];
   __shared__ double carry;
   double* ts = tile_sums + (int64_t)blockIdx.x * n_tiles;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   if (threadIdx.x == 0) carry = 0.0;
   __syncthreads();
   for (int base = 0; base < n_tiles; base += 1024) {
-    int idx = base + threadIdx.x;
-    double v = idx < n_tiles ? ts[idx] : 0.0;
-    buf[threadIdx.x] = v;
-    __syncthreads();
-    for (int off = 1; off < 1024; off <<= 1) {  // Hillis-Steele inclusive scan
-      double add = threadIdx.x >= off ? buf[threadIdx.x - off] : 0.0;
-      __syncthreads();
-      buf[threadIdx.x] += add;
-      __syncthreads();
+    const int idx = base + threadIdx.x;
+    const double v = idx < n_tiles ? ts[idx] : 0.0;
+    double incl = v;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const double n = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= off) incl += n;
     }
-    double incl = buf[threadIdx.x];
-    double c = carry;
-    if (idx < n_tiles) ts[idx] = c + incl - v;  // exclusive
+    if (lane == 31) wtot[wid] = incl;
     __syncthreads();
-    if (threadIdx.x == 1023) carry = c + incl;
+    if (wid == 0) {  // inclusive scan of the warp totals
+      double w = wtot[lane];
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const double n = __shfl_up_sync(0xffffffffu, w, off);
+        if (lane >= off) w += n;
+      }
+      wtot[lane] = w;
+    }
+    __syncthreads();
+    const double c = carry;
+    const double before = wid > 0 ? wtot[wid - 1] : 0.0;
+    if (idx < n_tiles) ts[idx] = c + before + incl - v;  // exclusive
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = c + before + incl;
     __syncthreads();
   }
   if (threadIdx.x == 0) totals[blockIdx.x] = carry;
 }
 
-// cdf[seg][i] = (tile_offset + inclusive in-tile prefix of |psi|^2) / total
-// (np.random.choice: cdf = p.cumsum(); cdf /= cdf[-1])
-__global__ void __launch_bounds__(kScanThreads)
-scan_write_cdf_kernel(const cplx* __restrict__ psi, int64_t dim, int64_t seg_stride, int n_tiles,
-                      const double* __restrict__ tile_offsets, const double* __restrict__ totals, double* cdf) {
-  __shared__ double warp_tot[kScanThreads / 32];
-  const cplx* p = psi + (int64_t)blockIdx.y * seg_stride;
-  double* c = cdf + (int64_t)blockIdx.y * dim;
-  const int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanItems;
+// In-tile part of the CDF, shared by the two sampling forms: value k of this thread is
+// cdf[base + k] = (tile_offset + inclusive in-tile prefix of |psi|^2) / total, in one fixed summation order
+// (np.random.choice: cdf = p.cumsum(); cdf /= cdf[-1]).  Needs kScanThreads threads and a shared double[8].
+__device__ __forceinline__ void tile_cdf_values(const cplx* __restrict__ p, int64_t dim, int64_t tile, double tile_offset,
+                                                double inv, double* warp_tot, double (&c)[kScanItems]) {
+  const int64_t base = tile * kScanTile + (int64_t)threadIdx.x * kScanItems;
   double v[kScanItems];
   double run = 0.0;
 #pragma unroll
@@ -257,12 +267,76 @@ scan_write_cdf_kernel(const cplx* __restrict__ psi, int64_t dim, int64_t seg_str
   __syncthreads();
   double wbase = 0.0;
   for (int w = 0; w < wid; ++w) wbase += warp_tot[w];
-  const double excl = wbase + incl - run + tile_offsets[(int64_t)blockIdx.y * n_tiles + blockIdx.x];
-  const double inv = 1.0 / totals[blockIdx.y];
+  const double excl = wbase + incl - run + tile_offset;
+#pragma unroll
+  for (int k = 0; k < kScanItems; ++k) c[k] = (excl + v[k]) * inv;
+}
+
+// cdf[seg][i] for every i: the form for batches of small states (the CDF of a task stays in L2 for its shots)
+__global__ void __launch_bounds__(kScanThreads)
+scan_write_cdf_kernel(const cplx* __restrict__ psi, int64_t dim, int64_t seg_stride, int n_tiles,
+                      const double* __restrict__ tile_offsets, const double* __restrict__ totals, double* cdf) {
+  __shared__ double warp_tot[kScanThreads / 32];
+  const cplx* p = psi + (int64_t)blockIdx.y * seg_stride;
+  double* c = cdf + (int64_t)blockIdx.y * dim;
+  double val[kScanItems];
+  tile_cdf_values(p, dim, blockIdx.x, tile_offsets[(int64_t)blockIdx.y * n_tiles + blockIdx.x], 1.0 / totals[blockIdx.y],
+                  warp_tot, val);
+  const int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanItems;
 #pragma unroll
   for (int k = 0; k < kScanItems; ++k) {
     int64_t i = base + k;
-    if (i < dim) c[i] = (excl + v[k]) * inv;
+    if (i < dim) c[i] = val[k];
+  }
+}
+
+// digits of configuration `lo` -> shots row (space.py:219-227; three-level projection h->0, r->1 when `project`)
+__device__ __forceinline__ void write_shot(int64_t lo, const uint32_t* __restrict__ configs, int n_atoms, int n_level,
+                                           int project, uint8_t* o) {
+  uint32_t cfg = configs ? configs[lo] : (uint32_t)lo;
+  for (int a = 0; a < n_atoms; ++a) {
+    uint32_t d = cfg % (uint32_t)n_level;
+    cfg /= (uint32_t)n_level;
+    if (project) d = (d == 2u) ? 1u : 0u;
+    o[a] = (uint8_t)d;
+  }
+}
+
+// The form for LARGE states with few shots (no CDF array: 8 bytes per amplitude less traffic and scratch): one CTA
+// per shot finds the tile by a binary search over the tile offsets and re-evaluates that tile's CDF values - the
+// same arithmetic as scan_write_cdf_kernel - to find the first index with cdf > u (searchsorted side="right").
+__global__ void __launch_bounds__(kScanThreads)
+sample_search_tiles_kernel(const cplx* __restrict__ psi, int64_t dim, int64_t seg_stride, int n_tiles,
+                           const double* __restrict__ tile_offsets, const double* __restrict__ totals,
+                           const uint32_t* __restrict__ configs, int n_atoms, int n_level, int project,
+                           const double* __restrict__ uniforms, int n_shots, uint8_t* shots) {
+  __shared__ double warp_tot[kScanThreads / 32];
+  __shared__ unsigned long long first;
+  const int seg = blockIdx.y, s = blockIdx.x;
+  const cplx* p = psi + (int64_t)seg * seg_stride;
+  const double* off = tile_offsets + (int64_t)seg * n_tiles;
+  const double total = totals[seg], inv = 1.0 / total;
+  const double u = uniforms[(int64_t)seg * n_shots + s];
+  // first tile whose end value (the offset of the next tile) exceeds u
+  int lo = 0, hi = n_tiles - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (off[mid + 1] * inv <= u) lo = mid + 1; else hi = mid;
+  }
+  if (threadIdx.x == 0) first = ~0ull;
+  double val[kScanItems];
+  tile_cdf_values(p, dim, lo, off[lo], inv, warp_tot, val);  // has a barrier after `first` is set
+  const int64_t base = (int64_t)lo * kScanTile + (int64_t)threadIdx.x * kScanItems;
+  unsigned long long mine = ~0ull;
+#pragma unroll
+  for (int k = kScanItems - 1; k >= 0; --k)
+    if (base + k < dim && val[k] > u) mine = (unsigned long long)(base + k);
+  if (mine != ~0ull) atomicMin(&first, mine);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int64_t idx = first == ~0ull ? ((int64_t)(lo + 1) * kScanTile) : (int64_t)first;  // rounding at a tile edge
+    if (idx >= dim) idx = dim - 1;
+    write_shot(idx, configs, n_atoms, n_level, project, shots + ((int64_t)seg * n_shots + s) * n_atoms);
   }
 }
 
@@ -281,14 +355,7 @@ __global__ void sample_search_kernel(const double* __restrict__ cdf, int64_t dim
       if (c[mid] <= u) lo = mid + 1; else hi = mid;
     }
     if (lo >= dim) lo = dim - 1;
-    uint32_t cfg = configs ? configs[lo] : (uint32_t)lo;
-    uint8_t* o = shots + ((int64_t)seg * n_shots + s) * n_atoms;
-    for (int a = 0; a < n_atoms; ++a) {
-      uint32_t d = cfg % (uint32_t)n_level;
-      cfg /= (uint32_t)n_level;
-      if (project) d = (d == 2u) ? 1u : 0u;
-      o[a] = (uint8_t)d;
-    }
+    write_shot(lo, configs, n_atoms, n_level, project, shots + ((int64_t)seg * n_shots + s) * n_atoms);
   }
 }
 

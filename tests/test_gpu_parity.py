@@ -277,13 +277,15 @@ def test_sampling_bit_exact_with_reference(name):
     assert np.array_equal(got, c.data["sample_shots"])
 
 
-def test_sampling_large_cdf_vs_numpy():
-    n = 20
+@pytest.mark.parametrize("n,shots", [(20, 5000), (22, 512)])
+def test_sampling_large_cdf_vs_numpy(n, shots):
+    """(20, 5000): CDF array + binary search; (22, 512): the two-level form for large states with few shots (tile
+    offsets searched, one tile re-evaluated per shot, no CDF array)"""
     dim = 1 << n
     rng = np.random.default_rng(11)
     psi = (rng.normal(size=dim) + 1j * rng.normal(size=dim)) * rng.random(dim) ** 4
     psi /= np.linalg.norm(psi)
-    u = rng.random(5000)
+    u = rng.random(shots)
     plan = _lib.Plan(n, 2, dim)
     got = plan.sample(psi, u)[0]
     cdf = np.cumsum(np.abs(psi) ** 2)
@@ -296,6 +298,24 @@ def test_sampling_large_cdf_vs_numpy():
     for s in bad:
         assert np.min(np.abs(cdf - u[s])) < 1e-12
     assert bad.size <= 2
+    plan.close()
+
+
+def test_sampling_more_states_than_one_grid_dimension():
+    """70 000 small states in one call: the segment dimension of the batched kernels is launched in chunks of 65 535"""
+    n, n_states, shots = 4, 70000, 3
+    dim = 1 << n
+    rng = np.random.default_rng(5)
+    psi = rng.normal(size=(n_states, dim)) + 1j * rng.normal(size=(n_states, dim))
+    u = rng.random((n_states, shots))
+    plan = _lib.Plan(n, 2, dim)
+    got = plan.sample(psi, u)
+    cdf = np.cumsum(np.abs(psi) ** 2, axis=1)
+    cdf /= cdf[:, -1:]
+    idx = (cdf[:, None, :] <= u[:, :, None]).sum(axis=2)
+    ref = ((idx[:, :, None] >> np.arange(n)[None, None, :]) & 1).astype(np.uint8)
+    assert (got != ref).any(axis=2).sum() <= 2
+    assert np.array_equal(got[-1], ref[-1]) and np.array_equal(got[65535], ref[65535])
     plan.close()
 
 
@@ -604,6 +624,37 @@ def test_large_streamed_evolve_norm_and_sharding_free_consistency():
     ref = oe.evolve(prog, atol=1e-9, rtol=1e-9)[-1]
     assert infidelity(out.data, ref) < 1e-8
     assert abs(np.linalg.norm(out.data) - 1.0) < 1e-6
+
+
+def test_streamed_full_protocol_16_atoms_matches_reference():
+    """The code path of BASELINE configs[3] (streamed engine + tiled H psi: both passes, ~18 000 dop853 steps at the
+    stability limit) over the FULL 4 us README protocol at the size the reference finishes in minutes: Square(4, 5.0),
+    2^16 amplitudes, run() defaults.  Golden = the reference's own final state (tests/golden/make_large_golden.py)."""
+    import json
+
+    from bloqade_analog_b200 import serialize
+
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "large_square4_a5.npz"))
+    with open(os.path.join(os.path.dirname(__file__), "golden", "large_square4_a5.json")) as f:
+        prog = serialize.program_from_dict(json.load(f))
+    h = RydbergHamiltonianCodeGen().emit(prog)
+    gate = AnalogGate(h)
+    (out,) = gate.apply(h.space.zero_state(np.complex128), engine="streamed")
+    ref = g["final_c64"].astype(np.complex128)
+    assert infidelity(out.data, ref) < 1e-8
+    assert abs(out.norm() - float(g["norm"])) < 1e-6
+    p = np.abs(out.data) ** 2
+    dens = np.array([p[(h.space.configurations >> a) & 1 == 1].sum() for a in range(16)])
+    np.testing.assert_allclose(dens, g["density"], rtol=0, atol=1e-6)
+    avg, var = h.average_and_variance(out)
+    ravg, rvar = g["avg_var"]
+    assert abs(avg - ravg) < 1e-5 * max(1.0, abs(ravg)) and abs(var - rvar) < 1e-5 * max(1.0, abs(rvar))
+    # seeded shots of the normalised state: the reference's own draws (np.random.choice consumes random_sample)
+    out.normalize()
+    shots = h.plan.sample(out.data, g["sample_uniforms"])
+    assert (shots.reshape(g["sample_shots"].shape) != g["sample_shots"]).any(axis=1).sum() <= 1
+    # the same evolution on the CTA-free gather RHS and on the tiled one is covered by
+    # test_streamed_engine_tiled_rhs_equals_gather_rhs
 
 
 def test_launch_counter_and_no_cpu_fallback():
