@@ -184,6 +184,9 @@ static int evolve_small_device(bqa_plan* p, const double* d_records, const int64
   // measured at dim 4096 (profiles/r02_summary.md): 512 threads x 8 elements with 128 registers per thread keep more
   // K-vector loads in flight than 1024 x 4 with 64 (75 vs 89 ms on the 148-task profile case); 256 x 16: 86 ms
   int threads = dim <= 256 ? 128 : (dim <= 1024 ? 256 : (dim <= 4096 ? 512 : 1024));
+  // blockade subspaces run the gather RHS (rhs_sub2_real / h_apply_element): a latency chain per element, more warps
+  // win (dim 2584: 12.7 us per RHS on 1024 threads, 18.6 on 512, 31 on 256; profiles/r02_summary.md)
+  if (!p->P.full_space && dim > 1024) threads = 1024;
   if (const char* e = getenv("BQA_SMALL_THREADS")) threads = atoi(e);  // measurement hook (profiles/r01_summary.md)
   const bool pair = getenv("BQA_SMALL_PAIR") != nullptr;
   if (use_cluster)

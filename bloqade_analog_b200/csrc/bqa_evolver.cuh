@@ -56,6 +56,7 @@ struct TaskEvolver {
   // two-level full space, no CSR term, Schroedinger picture, no phase waveform: contexts with kFastRhs evaluate
   // the RHS with their own fused routine (same arithmetic in the same order, so the results are bit-identical)
   bool fast_rhs;
+  bool sub_rhs;  // the same for a two-level blockade subspace (int32 gather partner table): Ctx::rhs_sub2_real
   bool coefs_ready = false;  // the shared coefficient scratch holds the values of time coefs_t
   double coefs_t = 0.0;
   int tab_n = 0;             // entries of w.coefs_tab valid for the current step
@@ -65,6 +66,8 @@ struct TaskEvolver {
       : ctx(ctx_), P(P_), tv(task_view(rec)), V(V_), w(w_), o(o_) {
     fast_rhs = P.full_space && P.n_level == 2 && P.n_csr == 0 && o.interaction == 0 && P.dim <= ((int64_t)1 << 30) &&
                !task_has_phase(tv);
+    sub_rhs = !P.full_space && P.n_level == 2 && P.n_csr == 0 && o.interaction == 0 && P.dim <= ((int64_t)1 << 28) &&
+              P.configs != nullptr && P.partners != nullptr && !task_has_phase(tv);
   }
 
   BQA_HD cplx* y() const { return w.vec[kVecY]; }
@@ -137,6 +140,11 @@ struct TaskEvolver {
     if constexpr (Ctx::kFastRhs) {
       if (fast_rhs) {
         ctx.rhs_full2_real(P.n_atoms, P.dim, cf, Vd, ys(), kout);
+        ctx.sync();
+        return;
+      }
+      if (sub_rhs) {
+        ctx.rhs_sub2_real(P.n_atoms, P.dim, cf, Vd, P.configs, P.partners, ys(), kout);
         ctx.sync();
         return;
       }

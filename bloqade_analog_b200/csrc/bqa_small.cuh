@@ -612,6 +612,89 @@ struct CtaCtxT {
     }
   }
 
+  // kout = -i H(t) ys for a two-level BLOCKADE SUBSPACE with real coefficients (TaskEvolver::sub_rhs): the same sums
+  // in the same order as h_apply_element<false, 2> (a real coefficient makes its complex multiply exact), organised
+  // like rhs_full2_real - four elements of a thread together, coefficients read once per atom, the configuration
+  // word and the static diagonal once per element, 32-bit indices, partner rows of the int32 gather table read
+  // coalesced through the read-only path, ys with ld.shared.  Reference: IndexMapping.matvec in a subspace
+  // (emulate/sparse_operator.py:99-128, emulate/ir/space.py:139-155).
+  template <bool kShared, int G>
+  __device__ __forceinline__ void rhs_sub2_real_impl(int n, uint32_t dim, const Coefs& C, const double* __restrict__ V,
+                                                     const uint32_t* __restrict__ configs,
+                                                     const int32_t* __restrict__ partners, const cplx* ys, cplx* kout) {
+    const uint32_t bd = blockDim.x;
+    const uint32_t sbase = kShared ? (uint32_t)__cvta_generic_to_shared(ys) : 0u;
+    auto load = [&](uint32_t idx) -> cplx {
+      if (kShared) {
+        cplx z;
+        asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(z.re), "=d"(z.im) : "r"(sbase + idx * 16u));
+        return z;
+      }
+      return ys[idx];
+    };
+    for (uint32_t i0 = threadIdx.x; i0 < dim; i0 += (uint32_t)G * bd) {
+      double ar[G], ai[G], dg[G];
+      uint32_t cfg[G];
+#pragma unroll
+      for (int j = 0; j < G; ++j) {
+        const uint32_t i = i0 + (uint32_t)j * bd;
+        ar[j] = 0.0;
+        ai[j] = 0.0;
+        cfg[j] = i < dim ? __ldg(configs + i) : 0u;
+        dg[j] = (V && i < dim) ? __ldg(V + i) : 0.0;
+      }
+#pragma unroll 2
+      for (int a = 0; a < n; ++a) {
+        const double cr = C.c_re[0][a], dl = C.delta[0][a];
+        const int32_t* __restrict__ row = partners + (size_t)a * dim;
+        int32_t pj[G];
+#pragma unroll
+        for (int j = 0; j < G; ++j) {
+          const uint32_t i = i0 + (uint32_t)j * bd;
+          pj[j] = i < dim ? __ldg(row + i) : -1;
+        }
+#pragma unroll
+        for (int j = 0; j < G; ++j) {
+          if ((cfg[j] >> a) & 1u) dg[j] -= dl;
+          if (pj[j] >= 0) {
+            const cplx z = load((uint32_t)pj[j]);
+            ar[j] += cr * z.re;
+            ai[j] += cr * z.im;
+          }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < G; ++j) {
+        const uint32_t i = i0 + (uint32_t)j * bd;
+        if (i < dim) {
+          const cplx zi = load(i);
+          kout[i] = times_minus_i(cmake(dg[j] * zi.re + ar[j], dg[j] * zi.im + ai[j]));
+        }
+      }
+    }
+  }
+  // elements of a thread that are evaluated together: all of them when a thread owns at most 4 (dim 2584 on 1024
+  // threads: 3, one trip through the atom loop), else trips of 4.  (Six together on 512 threads was measured SLOWER
+  // than two trips of 4: 24.3 vs 18.6 us per RHS at dim 2584; 1024 threads x 3: 12.7 us.)
+  template <bool kShared>
+  __device__ __forceinline__ void rhs_sub2_real_g(int n, uint32_t dim, const Coefs& C, const double* V, const uint32_t* configs,
+                                                  const int32_t* partners, const cplx* ys, cplx* kout) {
+    const uint32_t per = (dim + blockDim.x - 1) / blockDim.x;
+    if (per <= 2)
+      rhs_sub2_real_impl<kShared, 2>(n, dim, C, V, configs, partners, ys, kout);
+    else if (per == 3)
+      rhs_sub2_real_impl<kShared, 3>(n, dim, C, V, configs, partners, ys, kout);
+    else
+      rhs_sub2_real_impl<kShared, 4>(n, dim, C, V, configs, partners, ys, kout);
+  }
+  __device__ __forceinline__ void rhs_sub2_real(int n, int64_t dim, const Coefs& C, const double* V, const uint32_t* configs,
+                                                const int32_t* partners, const cplx* ys, cplx* kout) {
+    if (__isShared(ys))
+      rhs_sub2_real_g<true>(n, (uint32_t)dim, C, V, configs, partners, ys, kout);
+    else
+      rhs_sub2_real_g<false>(n, (uint32_t)dim, C, V, configs, partners, ys, kout);
+  }
+
   __device__ __forceinline__ void rhs_full2_real(int n, int64_t dim, const Coefs& C, const double* V, const cplx* ys,
                                                  cplx* kout) {
     if (exact_elems(dim) == 4 && n == kLog + 2 && __isShared(ys))

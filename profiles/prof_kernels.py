@@ -77,7 +77,7 @@ elif what in ("c1", "c2"):
     cg = RydbergHamiltonianCodeGen(CompileCache())
     hams = [cg.emit(p) for p in progs]
     res = {"what": what, "dim": int(hams[0].space.size), "tasks": len(hams)}
-    opts = _lib.make_opts("dop853", 1e-7, 1e-14)
+    opts = _lib.make_opts("dop853", 1e-7, 1e-14, engine=(sys.argv[2] if len(sys.argv) > 2 else "auto"))
     for rep in range(3):
         per = []
         t0 = time.perf_counter()
