@@ -112,6 +112,9 @@ static bool tiled_plan(int n_loc, int n_total, int64_t rank, const cplx* const* 
     } else {
       // `fresh` new atoms; the high group is widened downwards to at least 4 bits (lo_bits <= 9) over atoms
       // already done, which p0 then skips
+      // (sharing the remaining atoms evenly between the later passes of a sharded state - 13 + 7 + 7 instead of
+      // 13 + 10 + 4 at 27 local atoms, 1 KB rows instead of 128-byte ones over NVLink - was measured SLOWER on 8 GPUs:
+      // 13.8 against 12.9 ms at 30 atoms, profiles/r02_summary.md)
       const int fresh = std::min(n_tiled - next, maxfresh);
       const int tb = std::max(fresh, 4);
       s.lo_bits = kTileBits - tb;
@@ -161,8 +164,10 @@ static TiledKernel tiled_kernel_for(bool real, const TileSpec& s) {
 #define BQA_TILED_VARIANTS(K, R)                                                                          \
   K<R, false, false, 0>, K<R, false, true, 0>, K<R, false, false, 2>, K<R, false, true, 2>, K<R, false, false, 3>, \
       K<R, false, true, 3>, K<R, true, false, 0>, K<R, true, true, 0>
-  static const TiledKernel tab[16] = {BQA_TILED_VARIANTS(apply_tiled_kernel, false),
-                                      BQA_TILED_VARIANTS(apply_tiled_kernel, true)};
+#define BQA_TILED_REMOTE(K, R) K<R, false, true, 0, true>, K<R, false, true, 2, true>, K<R, false, true, 3, true>, K<R, true, true, 0, true>
+  static const TiledKernel tab[24] = {BQA_TILED_VARIANTS(apply_tiled_kernel, false),
+                                      BQA_TILED_VARIANTS(apply_tiled_kernel, true),
+                                      BQA_TILED_REMOTE(apply_tiled_kernel, false), BQA_TILED_REMOTE(apply_tiled_kernel, true)};
   static std::atomic<uint64_t> attr_set{0};
   if (!once_per_device(attr_set)) {
     for (TiledKernel k : tab)

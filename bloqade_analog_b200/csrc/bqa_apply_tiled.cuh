@@ -21,6 +21,7 @@
 // 375-398) with IndexMapping / CSR matvecs of bit-flip form (emulate/sparse_operator.py:24-34,99-128).
 #pragma once
 #include <cuda_runtime.h>
+#include <stdlib.h>
 
 #include "bqa_core.cuh"
 
@@ -151,7 +152,7 @@ __device__ __forceinline__ int64_t tile_seq(const TileSpec& S, int64_t it, int64
 // One kernel per variant (real / complex coefficients, first / later pass, leftover atom or not; the host picks):
 // operands that are kernel parameters stay in the constant bank, and every variant gets its own register
 // allocation - folded into one kernel, the variants spilled inside the tile loop.
-template <bool kReal, bool kFirst, bool kHasX, int kP0>
+template <bool kReal, bool kFirst, bool kHasX, int kP0, bool kRemX = false>
 __device__ __forceinline__ void apply_tiled_body(const int64_t dim, const int n, const double* __restrict__ V,
                                                  const TileSpec& S, const cplx* __restrict__ in,
                                                  cplx* __restrict__ out) {
@@ -205,6 +206,15 @@ __device__ __forceinline__ void apply_tiled_body(const int64_t dim, const int n,
     for (int p = 0; p < 9; ++p)
       if ((tid >> p) & 1) dl += sh.cf.delta[0][p];
   }
+  // kRemX (sharded state, the leftover atom is a rank bit): the partner amplitudes come from the PEER GPU over NVLink
+  // (~2 us away, L2 bypassed).  They are requested ONE QUAD AHEAD of the quad that uses them (xn), across tile
+  // boundaries, so the link always has one or two quads (32 - 64 KB per SM) in flight instead of a burst per quad.
+  cplx xn[kQuad];
+  if (kRemX) {
+    const cplx* x0 = S.x_ptr + tile_base(S, tile) + off0;
+#pragma unroll
+    for (int j = 0; j < kQuad; ++j) xn[j] = ldg_cplx(x0 + (size_t)j * stride);
+  }
   __syncthreads();
   for (;;) {
     const int64_t base = tile_base(S, tile);
@@ -242,7 +252,19 @@ __device__ __forceinline__ void apply_tiled_body(const int64_t dim, const int n,
           vq[j] = V ? ldg_f64(Vt + off, pol_once) : 0.0;
         else
           oq[j] = ldg_cplx(out_t + off, pol_once);
-        if (kHasX) xq[j] = ldg_cplx(xsrc + off, pol_psi);
+        if (kHasX && !kRemX) xq[j] = ldg_cplx(xsrc + off, pol_psi);
+      }
+      if (kRemX) {
+#pragma unroll
+        for (int j = 0; j < kQuad; ++j) xq[j] = xn[j];
+        if (g < kQuads - 1) {
+#pragma unroll
+          for (int j = 0; j < kQuad; ++j) xn[j] = ldg_cplx(xsrc + (size_t)((g + 1) * kQuad + j) * stride);
+        } else if (has_next) {
+          const cplx* xnext = S.x_ptr + tile_base(S, next) + off0;
+#pragma unroll
+          for (int j = 0; j < kQuad; ++j) xn[j] = ldg_cplx(xnext + (size_t)j * stride);
+        }
       }
       // a quarter of the next tile per quad, behind the latency-critical side streams (the whole tile at once
       // is a 96 KB burst per SM that the side streams then queue behind)
@@ -336,7 +358,7 @@ __device__ __forceinline__ void apply_tiled_body(const int64_t dim, const int n,
 
 // One CTA's share of a tiled pass: coefficients at time t, then the tile loop.  kReal is the host's promise that
 // no Rabi term of the record carries a phase waveform (record_has_phase), i.e. every c_im is exactly zero.
-template <bool kReal, bool kFirst, bool kHasX, int kP0>
+template <bool kReal, bool kFirst, bool kHasX, int kP0, bool kRemX = false>
 __device__ __forceinline__ void apply_tiled_cta(const PlanView& P, const double* __restrict__ rec,
                                                 const double* __restrict__ V, double t, const TileSpec& S,
                                                 const cplx* __restrict__ in, cplx* __restrict__ out) {
@@ -360,20 +382,22 @@ __device__ __forceinline__ void apply_tiled_cta(const PlanView& P, const double*
     sh.tabK[q] = d;
   }
   __syncthreads();
-  apply_tiled_body<kReal, kFirst, kHasX, kP0>(P.dim, n, V, S, in, out);
+  apply_tiled_body<kReal, kFirst, kHasX, kP0, kRemX>(P.dim, n, V, S, in, out);
 }
 
-template <bool kReal, bool kFirst, bool kHasX, int kP0>
+template <bool kReal, bool kFirst, bool kHasX, int kP0, bool kRemX = false>
 __global__ void __launch_bounds__(kTileThreads, 1)
 apply_tiled_kernel(const PlanView P, const double* __restrict__ rec, const double* __restrict__ V, double t,
                    const TileSpec S, const cplx* __restrict__ in, cplx* __restrict__ out) {
-  apply_tiled_cta<kReal, kFirst, kHasX, kP0>(P, rec, V, t, S, in, out);
+  apply_tiled_cta<kReal, kFirst, kHasX, kP0, kRemX>(P, rec, V, t, S, in, out);
 }
 
 // kernel variant index of a pass: 8 shapes {later p0 runtime, later p0 = 2, later p0 = 3, first} x {no x, x},
-// then real coefficients
+// then real coefficients; 16..23: the four shapes with a REMOTE leftover partner (complex, then real coefficients)
 inline int tiled_variant(bool real, const TileSpec& s) {
   const int shape = s.first ? 6 : (s.p0 == 2 ? 2 : (s.p0 == 3 ? 4 : 0));
+  // remote leftover partner (kRemX); BQA_NO_REMX: measurement hook, the partner is requested like a local one
+  if (s.n_x > 0 && s.x_ptr != nullptr && getenv("BQA_NO_REMX") == nullptr) return 16 + (real ? 4 : 0) + shape / 2;
   return (real ? 8 : 0) + shape + (s.n_x > 0 ? 1 : 0);
 }
 

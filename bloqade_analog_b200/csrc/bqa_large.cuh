@@ -235,12 +235,12 @@ __global__ void lg_abort_peers(const LgPeerFlags F, int world) {
 
 // K[dst] = f(t, ys) by one shared-memory-tiled pass (two-level full space, Schroedinger picture); the
 // first pass writes K[dst], later passes accumulate into it (bqa_apply_tiled.cuh)
-template <bool kReal, bool kFirst, bool kHasX, int kP0>
+template <bool kReal, bool kFirst, bool kHasX, int kP0, bool kRemX = false>
 __global__ void __launch_bounds__(kTileThreads, 1)
 lg_rhs_tiled(LargeCtrl* ctl, const PlanView P, const double* __restrict__ rec, const double* __restrict__ V, int tmode,
              int s, int dst, int cond, const TileSpec S) {
   if (!ctl->active || (cond == 1 && !ctl->accepted)) return;
-  apply_tiled_cta<kReal, kFirst, kHasX, kP0>(P, rec, V, lg_time(ctl, tmode, s), S, ctl->vec[kVecYs], ctl->vec[kVecK + dst]);
+  apply_tiled_cta<kReal, kFirst, kHasX, kP0, kRemX>(P, rec, V, lg_time(ctl, tmode, s), S, ctl->vec[kVecYs], ctl->vec[kVecK + dst]);
 }
 
 // hinit reductions: phase 0 -> (dnf, dny); phase 1 -> der2 with f1 = K[1]

@@ -14,7 +14,8 @@ struct LgRhsPlan {
 typedef void (*LgTiledKernel)(LargeCtrl*, const PlanView, const double*, const double*, int, int, int, int, const TileSpec);
 
 static LgTiledKernel lg_tiled_kernel_at(int variant) {
-  static const LgTiledKernel tab[16] = {BQA_TILED_VARIANTS(lg_rhs_tiled, false), BQA_TILED_VARIANTS(lg_rhs_tiled, true)};
+  static const LgTiledKernel tab[24] = {BQA_TILED_VARIANTS(lg_rhs_tiled, false), BQA_TILED_VARIANTS(lg_rhs_tiled, true),
+                                        BQA_TILED_REMOTE(lg_rhs_tiled, false), BQA_TILED_REMOTE(lg_rhs_tiled, true)};
   return tab[variant];
 }
 
@@ -140,7 +141,7 @@ static int evolve_large_run(bqa_plan* p, LgScratch& X, const double* d_records, 
   if (R.tiled) {
     static std::atomic<uint64_t> attr_set{0};
     if (!once_per_device(attr_set)) {
-      for (int v = 0; v < 16; ++v)
+      for (int v = 0; v < 24; ++v)
         CK(cudaFuncSetAttribute(lg_tiled_kernel_at(v), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTileDynSmem));
       once_per_device(attr_set, true);
     }

@@ -44,6 +44,13 @@ def split_sample_uniforms(uniforms: np.ndarray, shard_weights: Sequence[float]):
     return owner.astype(np.int64), np.clip(local, 0.0, np.nextafter(1.0, 0.0))
 
 
+def checkpoint_grid(duration: float, every: float):
+    """output times of evolve_checkpointed: every, 2 every, ... and the program duration itself as the last one
+    (a duration that is a whole multiple of `every` up to rounding must not leave a last segment of one ulp)"""
+    n = max(1, int(np.ceil(duration / every - 1e-9)))
+    return [every * k for k in range(1, n)] + [duration]
+
+
 class ShardedHamiltonian:
     """This rank's shard of `RydbergHamiltonian` for a two-level full-space program."""
 
@@ -169,14 +176,16 @@ class ShardedHamiltonian:
         psi = self._torch.from_numpy(np.load(self.checkpoint_path(directory))).to(f"cuda:{self.device}")
         return float(meta["t"]), psi
 
+    def checkpoint_grid(self, every: float):
+        return checkpoint_grid(float(self.program.duration), every)
+
     def evolve_checkpointed(self, directory: str, every: float, **solver):
         """AnalogGate._apply to the end of the program with a checkpoint every `every` microseconds of program time;
         resumes from `directory` when it holds a complete checkpoint.  SciPy's ode restarts the integrator at every
         output time (state_vector.py:589-600), so the segments ARE the reference's flow for times = the checkpoint
         grid: an interrupted and resumed run ends bit for bit like an uninterrupted one with the same grid.
         Returns (final shard, list of per-segment stats)."""
-        duration = float(self.program.duration)
-        grid = [min(duration, every * k) for k in range(1, int(np.ceil(duration / every)) + 1)]
+        grid = self.checkpoint_grid(every)
         t, psi, all_stats = 0.0, None, []
         loaded = self.load_checkpoint(directory)
         if loaded is not None:

@@ -134,7 +134,7 @@ def main():
     dist.broadcast_object_list(box, src=0)
     ck_dir = box[0]
     every = d / 3.0
-    grid = [min(d, every * k) for k in range(1, 4)]
+    grid = sh.checkpoint_grid(every)
     plain, _ = sh.evolve(grid)
     seg, _ = sh.evolve([grid[0]])
     sh.save_checkpoint(ck_dir, grid[0], seg[0])

@@ -39,3 +39,15 @@ def test_shardwise_sampling_equals_global_cdf_sampling(world):
         got[j] = owner[j] * ldim + min(np.searchsorted(c, lu[j] * c[-1], side="right"), ldim - 1)
     assert (got != ref).mean() < 2e-3  # only uniforms within rounding of a bin edge may differ
     assert np.all(p[got] > 0)
+
+
+def test_checkpoint_grid_has_no_one_ulp_segment():
+    """0.02 + 0.16 + 0.02 = 0.20000000000000004: three checkpoints of a third each must not leave a fourth segment
+    of one ulp (the integrator would end it with status -3)"""
+    from bloqade_analog_b200.sharded import checkpoint_grid
+
+    d = 0.02 + 0.16 + 0.02
+    g = checkpoint_grid(d, 0.2 / 3.0)
+    assert len(g) == 3 and g[-1] == d and g[0] < g[1] < g[2]
+    assert checkpoint_grid(1.0, 0.4) == [0.4, 0.8, 1.0]
+    assert checkpoint_grid(1.0, 2.0) == [1.0]
