@@ -128,6 +128,19 @@ lg_rhs(LargeCtrl* ctl, const PlanView P, const double* __restrict__ rec, const d
   }
 }
 
+// Interaction picture with the tiled RHS: the tiled passes apply the operator WITHOUT the static diagonal to
+// phi = u ys (lg_combine has rotated the stage input) and write -i (H - V) phi; this pass finishes
+// K[dst] = conj(u) * that, u = exp(-i V t)  (SV:342-359).  Multiplying by -i is exact, so conj(u) (-i z) has the bits of
+// -i (conj(u) z), the order of lg_rhs.
+__global__ void __launch_bounds__(kLgThreads)
+lg_rotate_conj(LargeCtrl* ctl, int64_t dim, const double* __restrict__ V, int tmode, int s, int dst, int cond) {
+  if (!ctl->active || (cond == 1 && !ctl->accepted)) return;
+  const double t = lg_time(ctl, tmode, s);
+  cplx* k = ctl->vec[kVecK + dst];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < dim; i += (int64_t)gridDim.x * blockDim.x)
+    k[i] = cmul_conj_a(phase_u(V[i], t), k[i]);
+}
+
 __device__ __forceinline__ void lg_store3(LargeCtrl* ctl, double a, double b, double c, double* red) {
   a = block_sum(a, red);
   b = block_sum(b, red);

@@ -9,6 +9,8 @@ struct LgRhsPlan {
   int world = 1;
   int tile_grid = 1;
   bool real = false;  // no phase waveform in the current task record: real-coefficient kernels
+  bool interaction = false;  // interaction picture: tiled passes without the static diagonal + lg_rotate_conj
+  int rot_grid = 1;
 };
 
 typedef void (*LgTiledKernel)(LargeCtrl*, const PlanView, const double*, const double*, int, int, int, int, const TileSpec);
@@ -31,8 +33,13 @@ static void lg_launch_rhs(bqa_plan* p, LargeCtrl* ctl, const double* rec, const 
   cudaStream_t s = p->stream;
   lg_sync_ranks(p, ctl, R);
   if (R.tiled) {
+    const bool rot = R.interaction && V != nullptr;
     for (const TileSpec& S : R.passes) {
-      lg_tiled_kernel_at(tiled_variant(R.real, S))<<<R.tile_grid, kTileThreads, kTileDynSmem, s>>>(ctl, p->P, rec, V, tmode, st, dst, cond, S);
+      lg_tiled_kernel_at(tiled_variant(R.real, S))<<<R.tile_grid, kTileThreads, kTileDynSmem, s>>>(ctl, p->P, rec, rot ? nullptr : V, tmode, st, dst, cond, S);
+      LAUNCHED();
+    }
+    if (rot) {
+      lg_rotate_conj<<<R.rot_grid, kLgThreads, 0, s>>>(ctl, p->P.dim, V, tmode, st, dst, cond);
       LAUNCHED();
     }
   } else {
@@ -132,7 +139,10 @@ static int evolve_large_run(bqa_plan* p, LgScratch& X, const double* d_records, 
   LgRhsPlan R;
   R.world = world;
   R.tile_grid = (int)std::min<int64_t>(std::max<int64_t>(dim >> kTileBits, 1), p->sm_count);
-  if (!o->interaction_picture && p->P.full_space && p->P.n_level == 2 && p->P.n_csr == 0 &&
+  R.interaction = o->interaction_picture != 0;
+  R.rot_grid = gs;
+  // (a sharded state stays in the Schroedinger picture: bqa_evolve_sharded refuses the interaction picture)
+  if ((!o->interaction_picture || !sh) && p->P.full_space && p->P.n_level == 2 && p->P.n_csr == 0 &&
       (sh || !getenv("BQA_NO_TILED")))
     R.tiled = tiled_plan(p->P.n_atoms, sh ? sh->n_total : p->P.n_atoms, sh ? sh->rank : 0, sh ? sh->partners : nullptr,
                          0, R.passes);

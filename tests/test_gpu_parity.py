@@ -614,6 +614,19 @@ def test_streamed_engine_tiled_rhs_equals_gather_rhs(monkeypatch):
     assert np.abs(a.data - b.data).max() < 1e-7
 
 
+def test_streamed_engine_interaction_picture_tiled_equals_gather(monkeypatch):
+    """interaction picture on the streamed engine: tiled passes without the static diagonal + the conj(u) rotation pass
+    against the gather RHS (BQA_NO_TILED), 2^16 state"""
+    prog = programs.adiabatic_program(ir.square_sites(4, 4, lattice_spacing=5.0), durations=[0.05, 0.3, 0.05])
+    h = RydbergHamiltonianCodeGen().emit(prog)
+    gate = AnalogGate(h)
+    (a,) = gate.apply(h.space.zero_state(np.complex128), engine="streamed", interaction_picture=True)
+    monkeypatch.setenv("BQA_NO_TILED", "1")
+    (b,) = gate.apply(h.space.zero_state(np.complex128), engine="streamed", interaction_picture=True)
+    assert infidelity(a.data, b.data) < 1e-12
+    assert np.abs(a.data - b.data).max() < 1e-7
+
+
 def test_large_streamed_evolve_norm_and_sharding_free_consistency():
     """2^20 state, short evolution on the streamed engine vs the CTA-free oracle (SciPy), fidelity < 1e-8"""
     from oracle import emulator as oe
@@ -624,6 +637,20 @@ def test_large_streamed_evolve_norm_and_sharding_free_consistency():
     ref = oe.evolve(prog, atol=1e-9, rtol=1e-9)[-1]
     assert infidelity(out.data, ref) < 1e-8
     assert abs(np.linalg.norm(out.data) - 1.0) < 1e-6
+
+
+def test_large_streamed_interaction_picture_vs_oracle():
+    """2^18 state, streamed engine in the INTERACTION picture (gather RHS with the exp(-i V t) rotation; at config-4-like
+    parameters it needs ~16x fewer RHS evaluations than the Schroedinger picture) against the oracle's restatement of
+    _ode_complex_kernel_int driven by SciPy (SV:342-359, 604-641) at the run() defaults"""
+    from oracle import emulator as oe
+
+    prog = programs.adiabatic_program(ir.square_sites(6, 3, lattice_spacing=5.0), [0.008, 0.064, 0.008])
+    h = RydbergHamiltonianCodeGen().emit(prog)
+    (out,) = AnalogGate(h).apply(h.space.zero_state(np.complex128), interaction_picture=True, engine="streamed")
+    ref = oe.evolve(prog, interaction_picture=True)[-1]
+    assert infidelity(out.data, ref) < 1e-8
+    assert np.abs(out.data - ref).max() < 1e-6
 
 
 def test_streamed_full_protocol_16_atoms_matches_reference():
