@@ -22,7 +22,7 @@ One JSON line on stdout (rank 0).
   cpu_baseline   the UNMODIFIED reference (baseline/_ref) on the host cores, bounded sample of the same sweep
   strong         (N > 1) ONE 4096-task sweep split over the ranks
   sharded        (N > 1) a (24 + log2 N)-atom state sharded over the ranks vs the unsharded run; N = 8: configs[4]
-  small_configs  configs[0] / configs[1] through .run()
+  small_configs  configs[0] / configs[1] (2a, 2b) through .run(); configs[3] end to end through .run(interaction_picture=True)
 `--impl reference` runs the unmodified reference through its own API and parallel path on the host cores.
 """
 import argparse
@@ -348,7 +348,7 @@ def hpsi_roofline(torch, device_index, peaks, peak_kind, n_atoms=25, reps=20):
     return res
 
 
-def small_config_lines(torch, ba, device):
+def small_config_lines(torch, ba, device, with_config4=True):
     """BASELINE configs[0] (C1, 6 tasks, 3x3 lattice) and configs[1] (C2, Chain(16) blockade subspace, D=2584)
     end to end through program.bloqade.python().run(100) on the B200 routine: seconds per call"""
     from bloqade.analog.atom_arrangement import Chain, Square
@@ -360,20 +360,35 @@ def small_config_lines(torch, ba, device):
           .detuning.uniform.piecewise_linear(du, de).batch_assign(a=list(np.arange(4.0, 7.0, 0.5))))
     c2 = (Chain(16, lattice_spacing=5.72).rydberg.rabi.amplitude.uniform.piecewise_linear(du, om)
           .detuning.uniform.piecewise_linear(du, de))
+    c2b = Chain(16, lattice_spacing=5.72).rydberg.detuning.uniform.piecewise_linear(du, de)
+    for i in range(16):  # sixteen local drives = sixteen IndexMapping terms in the reference (north_star's case)
+        c2b = c2b.amplitude.location(i).piecewise_linear(du, om)
+    # configs[3]: 5x5 lattice, full 2^25 space, ONE task, 1000 shots - in the interaction picture (the reference's own
+    # run() option): 6.6 k RHS evaluations instead of 315 k, seconds instead of minutes (profiles/r02_summary.md)
+    c4 = (Square(5, lattice_spacing=5.0).rydberg.rabi.amplitude.uniform.piecewise_linear(du, om)
+          .detuning.uniform.piecewise_linear(du, de))
     out = {}
-    for name, prog, kw in (("config1", c1, {}), ("config2a", c2, {"blockade_radius": 6.0})):
+    cases = [("config1", c1, {}, SHOTS, 3), ("config2a", c2, {"blockade_radius": 6.0}, SHOTS, 3),
+             ("config2b", c2b, {"blockade_radius": 6.0}, SHOTS, 3)]
+    if with_config4:
+        cases.append(("config4_interaction_picture", c4, {"interaction_picture": True}, 1000, 1))
+    for name, prog, kw, shots, reps in cases:
         r = routine.b200_routine(prog)
-        r.run(SHOTS, devices=[device], **kw, **SOLVER)
+        if reps > 1:
+            r.run(shots, devices=[device], **kw, **SOLVER)
         ts = []
-        for _ in range(3):
+        for _ in range(reps):
             torch.cuda.synchronize()
             t0 = time.perf_counter()
-            batch = r.run(SHOTS, devices=[device], **kw, **SOLVER)
+            batch = r.run(shots, devices=[device], **kw, **SOLVER)
             ts.append(time.perf_counter() - t0)
         n = len(batch.tasks)
         st = [t.integrator_stats for t in batch.tasks.values()]
-        out[name] = {"tasks": n, "s_per_run_call": float(np.median(ts)), "tasks_per_s": n / float(np.median(ts)),
+        out[name] = {"tasks": n, "shots": shots, "s_per_run_call": float(np.median(ts)), "tasks_per_s": n / float(np.median(ts)),
                      "rhs_evals": int(sum(int(s["nfcn"]) for s in st)), "lowering": routine.LAST_LOWERING}
+        if name.startswith("config4"):
+            bits = np.array(batch.report().bitstrings()[0])  # 0 = Rydberg in the report convention
+            out[name]["mean_rydberg_density"] = float(1.0 - bits.mean())
     return out
 
 
@@ -692,7 +707,7 @@ def gpu_arm(args):
     small = None
     if ba is not None and not args.no_small:
         try:
-            small = small_config_lines(torch, ba, local_rank)
+            small = small_config_lines(torch, ba, local_rank, with_config4=not args.no_c4)
         except Exception as e:  # noqa: BLE001
             small = {"error": repr(e)}
     cpu = None
@@ -741,6 +756,7 @@ def main():
     ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (N > 1)")
     ap.add_argument("--no-sharded", action="store_true", help="skip the sharded-state leg (N > 1)")
     ap.add_argument("--no-small", action="store_true", help="skip the configs[0]/configs[1] lines")
+    ap.add_argument("--no-c4", action="store_true", help="skip the configs[3] end-to-end run (interaction picture, ~25 s)")
     ap.add_argument("--hpsi-atoms", type=int, default=25)
     ap.add_argument("--no-hpsi", action="store_true")
     ap.add_argument("--engine", default="auto", choices=["auto", "cluster", "cta", "streamed"])
