@@ -57,6 +57,7 @@ struct TaskEvolver {
   // the RHS with their own fused routine (same arithmetic in the same order, so the results are bit-identical)
   bool fast_rhs;
   bool sub_rhs;  // the same for a two-level blockade subspace (int32 gather partner table): Ctx::rhs_sub2_real
+  bool fast_rhs_ip;  // fast_rhs's operator shape in the INTERACTION picture: the same routine on phi = u psi + rotation
   bool coefs_ready = false;  // the shared coefficient scratch holds the values of time coefs_t
   double coefs_t = 0.0;
   int tab_n = 0;             // entries of w.coefs_tab valid for the current step
@@ -66,6 +67,8 @@ struct TaskEvolver {
       : ctx(ctx_), P(P_), tv(task_view(rec)), V(V_), w(w_), o(o_) {
     fast_rhs = P.full_space && P.n_level == 2 && P.n_csr == 0 && o.interaction == 0 && P.dim <= ((int64_t)1 << 30) &&
                !task_has_phase(tv);
+    fast_rhs_ip = P.full_space && P.n_level == 2 && P.n_csr == 0 && o.interaction != 0 && P.dim <= ((int64_t)1 << 30) &&
+                  !task_has_phase(tv);
     sub_rhs = !P.full_space && P.n_level == 2 && P.n_csr == 0 && o.interaction == 0 && P.dim <= ((int64_t)1 << 28) &&
               P.configs != nullptr && P.partners != nullptr && !task_has_phase(tv);
   }
@@ -143,6 +146,11 @@ struct TaskEvolver {
         ctx.sync();
         return;
       }
+      if (fast_rhs_ip) {
+        ctx.rhs_full2_real(P.n_atoms, P.dim, cf, nullptr, ys(), kout, Vd, t);
+        ctx.sync();
+        return;
+      }
       if (sub_rhs) {
         ctx.rhs_sub2_real(P.n_atoms, P.dim, cf, Vd, P.configs, P.partners, ys(), kout);
         ctx.sync();
@@ -172,11 +180,11 @@ struct TaskEvolver {
     const double* Vd = V;
     const bool rot = rotating();
     if constexpr (Ctx::kFastRhs) {
-      if (!rot) {  // same sums in the same order, four elements per thread and the term loop outermost
-        ctx.stage_input_plain(P.dim, h, nnz, slot, val, kk, yy, out);
-        ctx.sync();
-        return;
-      }
+      // same sums in the same order, four elements per thread and the term loop outermost (+ the u(t) rotation in
+      // the interaction picture)
+      ctx.stage_input_plain(P.dim, h, nnz, slot, val, kk, yy, out, rot ? Vd : nullptr, t);
+      ctx.sync();
+      return;
     }
     ctx.for_each(P.dim, [&](int64_t i) {
       double sr = 0.0, si = 0.0;

@@ -526,9 +526,12 @@ struct CtaCtxT {
   // complex multiply by a real number and per-element coefficient loads).  A thread evaluates its (up to) four
   // elements together: coefficients are read once per atom, partner indices are 32-bit XORs, and ys - always
   // resident in shared memory for this engine - is read with ld.shared.
+  // Vrot != nullptr (interaction picture, V == nullptr): ys holds phi = u psi and the result is rotated back,
+  // kout = -i conj(u_i) (H - V) phi with u_i = exp(-i Vrot[i] t) - the arithmetic of the generic loop (SV:342-359).
   template <bool kShared>
   __device__ __forceinline__ void rhs_full2_real_impl(int n, uint32_t dim, const Coefs& C, const double* __restrict__ V,
-                                                      const cplx* ys, cplx* kout) {
+                                                      const cplx* ys, cplx* kout, const double* __restrict__ Vrot = nullptr,
+                                                      double t = 0.0) {
     const uint32_t bd = blockDim.x;
     const uint32_t sbase = kShared ? (uint32_t)__cvta_generic_to_shared(ys) : 0u;
     auto load = [&](uint32_t idx) -> cplx {
@@ -568,7 +571,9 @@ struct CtaCtxT {
         const uint32_t i = i0 + (uint32_t)j * bd;
         if (i < dim) {
           const cplx zi = load(i);
-          kout[i] = times_minus_i(cmake(dg[j] * zi.re + ar[j], dg[j] * zi.im + ai[j]));
+          cplx hz = cmake(dg[j] * zi.re + ar[j], dg[j] * zi.im + ai[j]);
+          if (Vrot) hz = cmul_conj_a(phase_u(__ldg(Vrot + i), t), hz);
+          kout[i] = times_minus_i(hz);
         }
       }
     }
@@ -577,9 +582,11 @@ struct CtaCtxT {
   // thread together, term loop outermost, so the vector pointer and the coefficient of a term are fetched once
   // per thread and four independent loads are in flight per term.  Per element the sum runs over j in the same
   // order as TaskEvolver::stage_input, so the result is bit-identical.
+  // Vrot != nullptr: the interaction-picture stage input, out = u (y + h sum), u_i = exp(-i Vrot[i] t) (SV:349-351)
   __device__ __forceinline__ void stage_input_plain(int64_t dim64, double h, int nnz, const int* slot, const double* val,
-                                                    cplx* const* kk, const cplx* yy, cplx* out) {
-    switch (exact_elems(dim64)) {
+                                                    cplx* const* kk, const cplx* yy, cplx* out,
+                                                    const double* __restrict__ Vrot = nullptr, double t = 0.0) {
+    switch (Vrot ? 0 : exact_elems(dim64)) {
       case 4: stage_input_exact<4, 4>(h, nnz, slot, val, kk, yy, out); return;
       case 8: stage_input_exact<8, kGC>(h, nnz, slot, val, kk, yy, out); return;
       case 16: stage_input_exact<16, kGC>(h, nnz, slot, val, kk, yy, out); return;
@@ -606,7 +613,8 @@ struct CtaCtxT {
         const uint32_t i = i0 + (uint32_t)e * bd;
         if (i < dim) {
           const cplx yz = yy[i];
-          out[i] = cmake(yz.re + h * sr[e], yz.im + h * si[e]);
+          const cplx z = cmake(yz.re + h * sr[e], yz.im + h * si[e]);
+          out[i] = Vrot ? cmul(phase_u(__ldg(Vrot + i), t), z) : z;
         }
       }
     }
@@ -696,7 +704,14 @@ struct CtaCtxT {
   }
 
   __device__ __forceinline__ void rhs_full2_real(int n, int64_t dim, const Coefs& C, const double* V, const cplx* ys,
-                                                 cplx* kout) {
+                                                 cplx* kout, const double* Vrot = nullptr, double t = 0.0) {
+    if (Vrot) {  // interaction picture
+      if (__isShared(ys))
+        rhs_full2_real_impl<true>(n, (uint32_t)dim, C, nullptr, ys, kout, Vrot, t);
+      else
+        rhs_full2_real_impl<false>(n, (uint32_t)dim, C, nullptr, ys, kout, Vrot, t);
+      return;
+    }
     if (exact_elems(dim) == 4 && n == kLog + 2 && __isShared(ys))
       rhs_exact<4, 4>(C, V, ys, kout);
     else if (exact_elems(dim) == 8 && n == kLog + 3 && __isShared(ys))
