@@ -187,6 +187,10 @@ static int evolve_small_device(bqa_plan* p, const double* d_records, const int64
   // blockade subspaces run the gather RHS (rhs_sub2_real / h_apply_element): a latency chain per element, more warps
   // win (dim 2584: 12.7 us per RHS on 1024 threads, 18.6 on 512, 31 on 256; profiles/r02_summary.md)
   if (!p->P.full_space && dim > 1024) threads = 1024;
+  // the plain step (interaction picture, dopri5, three-level atoms: no fused register-carry step) is a latency chain
+  // too: at dim 4096 1024 threads win (interaction-picture config-3 subset 226 against 241 ms; profiles/r01_summary.md
+  // had 127 against 143 ms for the plain Schroedinger step)
+  if (!fused && dim > 2048) threads = 1024;
   if (const char* e = getenv("BQA_SMALL_THREADS")) threads = atoi(e);  // measurement hook (profiles/r01_summary.md)
   const bool pair = getenv("BQA_SMALL_PAIR") != nullptr;
   if (use_cluster)
