@@ -57,6 +57,7 @@ struct TaskEvolver {
   // the RHS with their own fused routine (same arithmetic in the same order, so the results are bit-identical)
   bool fast_rhs;
   bool sub_rhs;  // the same for a two-level blockade subspace (int32 gather partner table): Ctx::rhs_sub2_real
+  bool fast_rhs_phase;  // the same operator shape with phase waveforms (complex coefficients), either picture
   bool fast_rhs_ip;  // fast_rhs's operator shape in the INTERACTION picture: the same routine on phi = u psi + rotation
   bool coefs_ready = false;  // the shared coefficient scratch holds the values of time coefs_t
   double coefs_t = 0.0;
@@ -67,6 +68,7 @@ struct TaskEvolver {
       : ctx(ctx_), P(P_), tv(task_view(rec)), V(V_), w(w_), o(o_) {
     fast_rhs = P.full_space && P.n_level == 2 && P.n_csr == 0 && o.interaction == 0 && P.dim <= ((int64_t)1 << 30) &&
                !task_has_phase(tv);
+    fast_rhs_phase = P.full_space && P.n_level == 2 && P.n_csr == 0 && P.dim <= ((int64_t)1 << 30) && task_has_phase(tv);
     fast_rhs_ip = P.full_space && P.n_level == 2 && P.n_csr == 0 && o.interaction != 0 && P.dim <= ((int64_t)1 << 30) &&
                   !task_has_phase(tv);
     sub_rhs = !P.full_space && P.n_level == 2 && P.n_csr == 0 && o.interaction == 0 && P.dim <= ((int64_t)1 << 28) &&
@@ -143,6 +145,12 @@ struct TaskEvolver {
     if constexpr (Ctx::kFastRhs) {
       if (fast_rhs) {
         ctx.rhs_full2_real(P.n_atoms, P.dim, cf, Vd, ys(), kout);
+        ctx.sync();
+        return;
+      }
+      if (fast_rhs_phase) {
+        const bool rotv = inter && Vd != nullptr;
+        ctx.rhs_full2_cplx(P.n_atoms, P.dim, cf, rotv ? nullptr : Vd, ys(), kout, rotv ? Vd : nullptr, t);
         ctx.sync();
         return;
       }

@@ -528,7 +528,9 @@ struct CtaCtxT {
   // resident in shared memory for this engine - is read with ld.shared.
   // Vrot != nullptr (interaction picture, V == nullptr): ys holds phi = u psi and the result is rotated back,
   // kout = -i conj(u_i) (H - V) phi with u_i = exp(-i Vrot[i] t) - the arithmetic of the generic loop (SV:342-359).
-  template <bool kShared>
+  // kCplx: drive coefficients with a phase waveform, c = c_re -+ i c_im (sign by the atom's bit), the expression of
+  // h_apply_element term for term.
+  template <bool kShared, bool kCplx = false>
   __device__ __forceinline__ void rhs_full2_real_impl(int n, uint32_t dim, const Coefs& C, const double* __restrict__ V,
                                                       const cplx* ys, cplx* kout, const double* __restrict__ Vrot = nullptr,
                                                       double t = 0.0) {
@@ -554,6 +556,7 @@ struct CtaCtxT {
 #pragma unroll 2
       for (int a = 0; a < n; ++a) {
         const double cr = C.c_re[0][a], dl = C.delta[0][a];
+        const double cim = kCplx ? C.c_im[0][a] : 0.0;
         const uint32_t bit = 1u << a;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -561,8 +564,14 @@ struct CtaCtxT {
           if (i < dim) {
             if (i & bit) dg[j] -= dl;
             const cplx z = load(i ^ bit);
-            ar[j] += cr * z.re;
-            ai[j] += cr * z.im;
+            if (kCplx) {
+              const double ci = (i & bit) ? cim : -cim;
+              ar[j] += cr * z.re - ci * z.im;
+              ai[j] += cr * z.im + ci * z.re;
+            } else {
+              ar[j] += cr * z.re;
+              ai[j] += cr * z.im;
+            }
           }
         }
       }
@@ -701,6 +710,15 @@ struct CtaCtxT {
       rhs_sub2_real_g<true>(n, (uint32_t)dim, C, V, configs, partners, ys, kout);
     else
       rhs_sub2_real_g<false>(n, (uint32_t)dim, C, V, configs, partners, ys, kout);
+  }
+
+  // the same routine for coefficients with a phase (either picture)
+  __device__ __forceinline__ void rhs_full2_cplx(int n, int64_t dim, const Coefs& C, const double* V, const cplx* ys,
+                                                 cplx* kout, const double* Vrot = nullptr, double t = 0.0) {
+    if (__isShared(ys))
+      rhs_full2_real_impl<true, true>(n, (uint32_t)dim, C, V, ys, kout, Vrot, t);
+    else
+      rhs_full2_real_impl<false, true>(n, (uint32_t)dim, C, V, ys, kout, Vrot, t);
   }
 
   __device__ __forceinline__ void rhs_full2_real(int n, int64_t dim, const Coefs& C, const double* V, const cplx* ys,
