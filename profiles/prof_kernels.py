@@ -3,6 +3,7 @@
    python profiles/prof_kernels.py streamed  [n_atoms=25]   a few dop853 steps of the streamed engine (combine / error kernels)
    python profiles/prof_kernels.py c1                       BASELINE configs[0]: 6 tasks of the 3x3 lattice (cluster engine)
    python profiles/prof_kernels.py c2                       BASELINE configs[1]: Chain(16) blockade subspace, D = 2584
+   python profiles/prof_kernels.py three_level [n=8] [tasks=148]   three-level (hyperfine) atoms: Chain(n), D = 3^n, a sweep batch
 Prints one JSON line with CUDA-event timings (torch events on the plan's stream)."""
 import json
 import os
@@ -96,3 +97,22 @@ elif what in ("c1", "c2"):
         res["rhs_total"] = nf
         res["us_per_rhs"] = 1e3 * sum(per) / nf
     print(json.dumps(res))
+elif what == "three_level":
+    n = int(sys.argv[2]) if len(sys.argv) > 2 else 8
+    n_tasks = int(sys.argv[3]) if len(sys.argv) > 3 else 148
+    progs = [programs.adiabatic_program(ir.chain_sites(n, lattice_spacing=5.72), durations=[0.05, 0.4, 0.05],
+                                        delta=[-16.33, -16.33, 4.0 + 0.1 * k, 4.0 + 0.1 * k], atom_type=ir.ThreeLevelAtom)
+             for k in range(n_tasks)]
+    cg = RydbergHamiltonianCodeGen(CompileCache())
+    hams = [cg.emit(p) for p in progs]
+    plan = hams[0].plan
+    blob, off = concat_records([h.record for h in hams])
+    times = np.array([[h.emulator_ir.duration] for h in hams])
+    opts = _lib.make_opts("dop853", 1e-7, 1e-14)
+    plan.enable_timing(True)
+    out, st = plan.evolve_batch(blob, off, times, opts)
+    ms, k = plan.get_timing()
+    print(json.dumps({"what": what, "n_atoms": n, "dim": int(hams[0].space.size), "tasks": n_tasks, "kernel_ms": ms,
+                      "tasks_per_s": 1e3 * n_tasks / ms, "mean_rhs_per_task": float(st["nfcn"].mean()),
+                      "failed": int((st["status"].reshape(-1) != 1).sum()),
+                      "alg_GBps": 32.0 * hams[0].space.size * float(st["nfcn"].sum()) / ms / 1e6}))
