@@ -228,7 +228,16 @@ static int pick_engine(const bqa_plan* p, const bqa_solver_opts* o, int n_tasks)
   // measured on B200 (profiles/r01_summary.md): with all vectors on chip the cluster engine is 1.5-2.2x faster
   // than the CTA-per-task kernel while one or two CTAs hold a task (dim <= 2048 for dop853); at 4 CTAs per task
   // (dim 4096) the DSMEM gathers and cluster barriers cost more than the CTA kernel's L2 traffic (-10 %)
-  if (cluster_fit(p, p->P.dim, o->solver == BQA_SOLVER_DOPRI5 ? 9 : 12, &cs, &ch) && cs <= 2) return BQA_ENGINE_CLUSTER;
+  if (cluster_fit(p, p->P.dim, o->solver == BQA_SOLVER_DOPRI5 ? 9 : 12, &cs, &ch) && cs <= 2) {
+    // outside the cluster engine's fused dop853 path (interaction picture, dopri5, subspaces, three-level atoms) it
+    // gathers through DSMEM with the generic loop, and from dim 1024 on the CTA engine's fused RHS routines win
+    // (296 tasks: 10 atoms 12.8 against 16.1 ms in the interaction picture, 13.5 against 31.8 ms with dopri5; 11 atoms
+    // 19.7 / 39.4 and 27.5 / 88.0 ms; 8 - 9 atoms the cluster engine stays ahead; profiles/r02_small_ip_engines.txt)
+    const bool cluster_fast = p->P.full_space && p->P.n_level == 2 && p->P.n_csr == 0 && !o->interaction_picture &&
+                              o->solver == BQA_SOLVER_DOP853;
+    if (cluster_fast || p->P.dim < 1024) return BQA_ENGINE_CLUSTER;
+    return BQA_ENGINE_CTA_PER_TASK;
+  }
   if (p->P.dim <= 8192) return BQA_ENGINE_CTA_PER_TASK;
   if ((int64_t)n_tasks >= p->sm_count && p->P.dim <= 65536) return BQA_ENGINE_CTA_PER_TASK;
   return BQA_ENGINE_STREAMED;
